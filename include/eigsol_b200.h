@@ -220,6 +220,14 @@ EIGSOL_B200_API int eigsol_b200_halo_plan(int64_t row_count, const int32_t* rowp
 EIGSOL_B200_API int eigsol_b200_choose_kernel(int dtype, int64_t rows, const int32_t* rowptr,
                                               int* kernel_out, int* lanes_out);
 
+/* The start vector of power_method.hpp:62 -- Vector<Scalar>::Random(n) followed by normalize() --
+ * restated on the host for callers that have no Eigen (the Python mirror): draws from libc rand()
+ * exactly as eigen/Eigen/src/Core/RandomImpl.h:46-51,66-69,89-99 does (two 31-bit rand() words per
+ * double, value in [-1,1); complex = imaginary part drawn first, as g++ evaluates the constructor
+ * arguments of RandomImpl.h:256), then divides by the 2-norm (eigen/Eigen/src/Core/Dot.h:110-114).
+ * seed >= 0: srand(seed) first; seed < 0: continue the caller's rand() stream. */
+EIGSOL_B200_API int eigsol_b200_random_unit(int dtype, int64_t n, int seed, void* x_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,1167 @@
+// engine.cu -- host runtime + C ABI of libeigsol_b200.so (see include/eigsol_b200.h).
+//
+// Replaces the loop of EigSol::powerMethodImpl (reference: src/power_method/power_method.hpp:61-98)
+// by launches of the fused kernels in kernels.cuh.  The host side here only plans (plan.hpp), uploads,
+// issues launches and polls the device-resident PowerState; no arithmetic of the path runs on the CPU
+// and there is no CPU fallback: without a CUDA device every compute entry point fails loudly.
+#include <algorithm>
+#include <climits>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/eigsol_b200.h"
+#include "kernels.cuh"
+#include "plan.hpp"
+#include "runtime.hpp"
+
+namespace eigsol_b200 {
+
+static thread_local std::string g_last_error;
+
+// -------------------------------------------------------------------------------------------------
+// One rank of a multi-GPU group.
+// -------------------------------------------------------------------------------------------------
+struct Comm {
+    int rank = 0, nranks = 1, device = 0;
+    ncclComm_t nccl_comm = nullptr;
+    cudaStream_t stream = nullptr;
+    DevBuf scratch;  // small device scratch for setup-time collectives
+    ~Comm() {
+        if (nccl_comm) nccl().CommDestroy(nccl_comm);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+static int env_int(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return v && *v ? std::atoi(v) : dflt;
+}
+
+static void require_device() {
+    int n = 0;
+    const cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        throw DeviceError(std::string("powerMethod: device error: no CUDA device available (") +
+                          (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                          "); this path has no CPU fallback");
+    }
+}
+
+// all-gather of one int64 per rank (setup only)
+static std::vector<int64_t> comm_allgather_i64(Comm* c, int64_t v) {
+    std::vector<int64_t> out(size_t(c->nranks), 0);
+    if (c->nranks == 1) {
+        out[0] = v;
+        return out;
+    }
+    int64_t* d = c->scratch.as<int64_t>();
+    EIGSOL_CUDA(cudaMemcpyAsync(d + c->nranks + c->rank, &v, sizeof v, cudaMemcpyHostToDevice, c->stream));
+    // AllGather may be absent from a very old libnccl; grouped broadcasts are equivalent
+    EIGSOL_NCCL(nccl().GroupStart());
+    for (int r = 0; r < c->nranks; ++r)
+        EIGSOL_NCCL(nccl().Broadcast(d + c->nranks + c->rank, d + r, 1, ncclInt64, r, c->nccl_comm, c->stream));
+    EIGSOL_NCCL(nccl().GroupEnd());
+    EIGSOL_CUDA(cudaMemcpyAsync(out.data(), d, sizeof(int64_t) * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
+    return out;
+}
+
+// -------------------------------------------------------------------------------------------------
+// The device-resident matrix + iteration state behind an eigsol_b200_matrix handle.
+// -------------------------------------------------------------------------------------------------
+struct MatrixImpl {
+    int dtype = 0;
+    bool dense = false;
+    int64_t n = 0, nnz_global = 0;
+    Comm* comm = nullptr;
+    int rank = 0, nranks = 1, device = 0, sm_count = 148;
+
+    // partition and halo
+    std::vector<int64_t> row_begin;
+    int64_t lo = 0, hi = 0, nloc = 0, nloc_pad = 0, nhalo = 0, ext_len = 0, local_nnz = 0;
+    HaloPlan halo;
+    std::vector<int64_t> send_count, send_off, send_start;  // per peer
+    std::vector<char> send_contig;
+    bool need_pack = false;
+    DevBuf d_send_idx, d_sendbuf;
+
+    // sparse layouts
+    CsrHost csr;  // local rows, localized columns (kept on the host to rebuild layouts)
+    RowStats stats;
+    DevBuf d_rowptr, d_colidx, d_vals;
+    DevBuf d_sell_off, d_sell_col, d_sell_val;
+    int sell_R = 0;
+    int64_t sell_nslices = 0, sell_padded = 0;
+    DevBuf d_rowblk;
+    int nblk = 0;
+
+    // dense layout
+    DevBuf d_dense, d_dense_partial, d_tile_ticket;
+    int64_t lda = 0;
+    int nseg = 1, ntiles = 1;
+
+    // vectors and state
+    DevBuf buf[2], d_state, d_partials, d_scal, d_xloc, d_xglob;
+    PinnedBuf h_state;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    // launch configuration
+    int kernel = K_CSR_SCALAR, lanes = 0, grid = 1, block = 256, nslots = 1;
+    int64_t stored_bytes = 0;
+    int64_t launches = 0;  // kernel launches issued over the handle's life
+    int issued = 0;        // matvec launches issued since begin (buffer parity on the host)
+    bool begun = false;
+    int max_trips = 0;
+    cudaGraphExec_t graph = nullptr;
+    int graph_len = 0;
+
+    int ss() const { return dtype ? 16 : 8; }
+    ~MatrixImpl() {
+        if (graph) cudaGraphExecDestroy(graph);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+
+    void init_common(int dtype_, Comm* comm_);
+    void init_sparse_local(CsrHost&& local_global_cols);
+    void init_dense(int64_t rows, const void* a, int64_t lda_host);
+    void plan_exchange();
+    void alloc_vectors();
+    void set_kernel(int kernel_, int lanes_);
+    void configure_launch();
+    void drop_graph();
+
+    void begin(const void* x0, int max_it, double tol);
+    void exchange_halo(int in);
+    void launch_matvec(int fused);
+    void issue_trips(int k);
+    void step(int trips, float* ms_out);
+    void end(void* x_out, double lambda_out[2], int* iters, int* conv);
+    const PowerState& poll_state();
+    void gather_download(const void* d_local, void* host_out);
+    void run(const void* x0, int max_it, double tol, void* x_out, double lambda_out[2], int* iters, int* conv);
+    void matvec(const void* x, void* y);
+    void fill_info(eigsol_b200_matrix_info* info) const;
+};
+
+void MatrixImpl::init_common(int dtype_, Comm* comm_) {
+    require_device();
+    dtype = dtype_;
+    comm = comm_;
+    if (comm) {
+        rank = comm->rank;
+        nranks = comm->nranks;
+        device = comm->device;
+        EIGSOL_CUDA(cudaSetDevice(device));
+    } else {
+        EIGSOL_CUDA(cudaGetDevice(&device));
+    }
+    cudaDeviceProp prop;
+    EIGSOL_CUDA(cudaGetDeviceProperties(&prop, device));
+    sm_count = prop.multiProcessorCount;
+    EIGSOL_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    EIGSOL_CUDA(cudaEventCreate(&ev0));
+    EIGSOL_CUDA(cudaEventCreate(&ev1));
+    d_state.alloc(sizeof(PowerState));
+    d_scal.alloc(4 * sizeof(double));
+    h_state.alloc(sizeof(PowerState));
+}
+
+void MatrixImpl::alloc_vectors() {
+    nloc_pad = (nloc + 15) / 16 * 16;
+    ext_len = nloc_pad + nhalo;
+    for (auto& b : buf) b.alloc(size_t(ext_len) * ss(), 256);
+    d_xloc.alloc(size_t(std::max<int64_t>(nloc, 1)) * ss());
+    d_xglob.alloc(size_t(std::max<int64_t>(n, 1)) * ss());
+}
+
+// -------------------------------------------------------------------------------------------------
+// Exchange plan: tell every peer which of its entries this rank reads each iteration (setup only).
+// After this, send_count[q]/d_send_idx describe what to send to q, halo.peer_off what arrives from q.
+// -------------------------------------------------------------------------------------------------
+void MatrixImpl::plan_exchange() {
+    send_count.assign(size_t(nranks), 0);
+    send_off.assign(size_t(nranks) + 1, 0);
+    send_start.assign(size_t(nranks), 0);
+    send_contig.assign(size_t(nranks), 1);
+    need_pack = false;
+    if (nranks == 1) return;
+    Comm* c = comm;
+    int64_t* d = c->scratch.as<int64_t>();
+    // counts: d[0..P) = what I need from each peer, d[P..2P) = what each peer needs from me
+    EIGSOL_CUDA(cudaMemcpyAsync(d, halo.peer_count.data(), sizeof(int64_t) * nranks, cudaMemcpyHostToDevice, c->stream));
+    EIGSOL_NCCL(nccl().GroupStart());
+    for (int q = 0; q < nranks; ++q) {
+        if (q == rank) continue;
+        EIGSOL_NCCL(nccl().Send(d + q, 1, ncclInt64, q, c->nccl_comm, c->stream));
+        EIGSOL_NCCL(nccl().Recv(d + nranks + q, 1, ncclInt64, q, c->nccl_comm, c->stream));
+    }
+    EIGSOL_NCCL(nccl().GroupEnd());
+    EIGSOL_CUDA(cudaMemcpyAsync(send_count.data(), d + nranks, sizeof(int64_t) * nranks, cudaMemcpyDeviceToHost, c->stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
+    send_count[rank] = 0;
+    for (int q = 0; q < nranks; ++q) send_off[q + 1] = send_off[q] + send_count[q];
+    const int64_t total_send = send_off[nranks];
+
+    DevBuf d_need;  // my halo columns (global), grouped by owner
+    d_need.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(nhalo, 1)));
+    d_need.upload(halo.cols.data(), sizeof(int32_t) * size_t(nhalo), c->stream);
+    d_send_idx.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(total_send, 1)));
+    EIGSOL_NCCL(nccl().GroupStart());
+    for (int q = 0; q < nranks; ++q) {
+        if (q == rank) continue;
+        if (halo.peer_count[q] > 0)
+            EIGSOL_NCCL(nccl().Send(d_need.as<int32_t>() + halo.peer_off[q], size_t(halo.peer_count[q]), ncclInt32, q,
+                                    c->nccl_comm, c->stream));
+        if (send_count[q] > 0)
+            EIGSOL_NCCL(nccl().Recv(d_send_idx.as<int32_t>() + send_off[q], size_t(send_count[q]), ncclInt32, q,
+                                    c->nccl_comm, c->stream));
+    }
+    EIGSOL_NCCL(nccl().GroupEnd());
+    std::vector<int32_t> idx(size_t(total_send), 0);
+    if (total_send)
+        EIGSOL_CUDA(cudaMemcpyAsync(idx.data(), d_send_idx.p, sizeof(int32_t) * size_t(total_send), cudaMemcpyDeviceToHost,
+                                    c->stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
+    // global -> local numbering; a contiguous ascending run is sent straight from the vector
+    for (int q = 0; q < nranks; ++q) {
+        bool contig = true;
+        for (int64_t k = send_off[q]; k < send_off[q + 1]; ++k) {
+            if (idx[k] < lo || idx[k] >= hi) throw PlanError("peer requested a column this rank does not own");
+            idx[k] = int32_t(idx[k] - lo);
+            if (k > send_off[q] && idx[k] != idx[k - 1] + 1) contig = false;
+        }
+        send_contig[q] = contig ? 1 : 0;
+        send_start[q] = send_count[q] ? idx[send_off[q]] : 0;
+        if (!contig) need_pack = true;
+    }
+    if (total_send) {
+        EIGSOL_CUDA(cudaMemcpy(d_send_idx.p, idx.data(), sizeof(int32_t) * size_t(total_send), cudaMemcpyHostToDevice));
+        d_sendbuf.alloc(size_t(total_send) * ss());
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// Sparse: local rows in CSR with GLOBAL columns -> halo plan, localized columns, layouts, vectors.
+// row_begin must be set.
+// -------------------------------------------------------------------------------------------------
+void MatrixImpl::init_sparse_local(CsrHost&& a) {
+    dense = false;
+    lo = row_begin[rank];
+    hi = row_begin[rank + 1];
+    nloc = hi - lo;
+    if (a.rows != nloc) throw PlanError("row block size does not match the partition");
+    csr = std::move(a);
+    local_nnz = csr.nnz();
+    halo = halo_plan(nloc, csr.rowptr.data(), csr.colidx.data(), row_begin, rank);
+    nhalo = int64_t(halo.cols.size());
+    alloc_vectors();
+    if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
+    localize_columns(local_nnz, csr.colidx.data(), lo, hi, nloc_pad, halo.cols);
+    csr.cols = ext_len;
+    plan_exchange();
+    stats = row_stats(nloc, csr.rowptr.data());
+    if (nranks > 1) {
+        const std::vector<int64_t> all = comm_allgather_i64(comm, local_nnz);
+        nnz_global = 0;
+        for (int64_t v : all) nnz_global += v;
+    } else {
+        nnz_global = local_nnz;
+    }
+    // CSR arrays are always resident (scalar / vector / stream variants share them)
+    d_rowptr.alloc(sizeof(int32_t) * size_t(nloc + 1));
+    d_rowptr.upload(csr.rowptr.data(), sizeof(int32_t) * size_t(nloc + 1), stream);
+    d_colidx.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(local_nnz, 1)));
+    d_colidx.upload(csr.colidx.data(), sizeof(int32_t) * size_t(local_nnz), stream);
+    d_vals.alloc(size_t(std::max<int64_t>(local_nnz, 1)) * ss());
+    d_vals.upload(csr.vals.data(), size_t(local_nnz) * ss(), stream);
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    const int forced = env_int("EIGSOL_B200_KERNEL", 0);
+    const KernelChoice ch = choose_kernel(dtype, stats);
+    if (forced > 0 && forced <= K_SELL) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
+    else set_kernel(ch.kernel, ch.lanes);
+}
+
+void MatrixImpl::drop_graph() {
+    if (graph) cudaGraphExecDestroy(graph);
+    graph = nullptr;
+    graph_len = 0;
+}
+
+void MatrixImpl::set_kernel(int kernel_, int lanes_) {
+    drop_graph();
+    if (dense) {
+        kernel = K_GEMV;
+        lanes = 0;
+        configure_launch();
+        return;
+    }
+    if (kernel_ == K_AUTO) {
+        const KernelChoice ch = choose_kernel(dtype, stats);
+        kernel_ = ch.kernel;
+        lanes_ = ch.lanes;
+    }
+    if (kernel_ < K_CSR_SCALAR || kernel_ > K_SELL) throw PlanError("unknown sparse kernel id");
+    if (kernel_ == K_CSR_VECTOR) {
+        if (lanes_ == 0) lanes_ = 8;
+        if (lanes_ != 2 && lanes_ != 4 && lanes_ != 8 && lanes_ != 16 && lanes_ != 32)
+            throw PlanError("CSR_VECTOR lanes per row must be 2, 4, 8, 16 or 32");
+    } else if (kernel_ == K_SELL) {
+        if (lanes_ == 0) lanes_ = dtype ? 1 : 2;
+        if (lanes_ != 1 && lanes_ != 2) throw PlanError("SELL rows per lane must be 1 or 2");
+        if (csr.rowptr.empty()) throw StateError("host CSR copy was released; SELL layout cannot be rebuilt");
+        if (sell_R != lanes_) {
+            SellHost s = build_sell(csr, lanes_);
+            sell_R = lanes_;
+            sell_nslices = s.nslices;
+            sell_padded = s.padded();
+            d_sell_off.alloc(sizeof(int64_t) * size_t(s.nslices + 1));
+            d_sell_off.upload(s.slice_off.data(), sizeof(int64_t) * size_t(s.nslices + 1), stream);
+            d_sell_col.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(sell_padded, 1)));
+            d_sell_col.upload(s.colidx.data(), sizeof(int32_t) * size_t(sell_padded), stream);
+            d_sell_val.alloc(size_t(std::max<int64_t>(sell_padded, 1)) * ss());
+            d_sell_val.upload(s.vals.data(), size_t(sell_padded) * ss(), stream);
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        }
+    } else if (kernel_ == K_CSR_STREAM) {
+        lanes_ = 0;
+        if (nblk == 0 && nloc > 0) {
+            if (csr.rowptr.empty()) throw StateError("host CSR copy was released; row blocks cannot be rebuilt");
+            const int tile = dtype ? StreamCfg<double2>::TILE : StreamCfg<double>::TILE;
+            std::vector<int32_t> rb = build_row_blocks(nloc, csr.rowptr.data(), tile, kStreamMaxRows);
+            nblk = int(rb.size()) - 1;
+            d_rowblk.alloc(sizeof(int32_t) * rb.size());
+            d_rowblk.upload(rb.data(), sizeof(int32_t) * rb.size(), stream);
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        }
+    } else {
+        lanes_ = 0;
+    }
+    kernel = kernel_;
+    lanes = lanes_;
+    configure_launch();
+}
+
+// -------------------------------------------------------------------------------------------------
+// Dense: rows [lo, hi) of the column-major host matrix, columns re-ordered into the rank's extended
+// numbering [own columns | gap | remote columns ascending] so the kernel sees a plain GEMV against
+// the extended vector.
+// -------------------------------------------------------------------------------------------------
+void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
+    dense = true;
+    n = rows;
+    nnz_global = n * n;
+    row_begin = partition_even(n, nranks);
+    lo = row_begin[rank];
+    hi = row_begin[rank + 1];
+    nloc = hi - lo;
+    local_nnz = nloc * n;
+    halo = HaloPlan();
+    halo.peer_count.assign(size_t(nranks), 0);
+    halo.peer_off.assign(size_t(nranks) + 1, 0);
+    if (nranks > 1) {
+        for (int64_t c = 0; c < n; ++c)
+            if (c < lo || c >= hi) halo.cols.push_back(int32_t(c));
+        for (int q = 0; q < nranks; ++q) halo.peer_count[q] = q == rank ? 0 : row_begin[q + 1] - row_begin[q];
+        for (int q = 0; q < nranks; ++q) halo.peer_off[q + 1] = halo.peer_off[q] + halo.peer_count[q];
+    }
+    nhalo = int64_t(halo.cols.size());
+    alloc_vectors();
+    plan_exchange();
+    stats = RowStats();
+    stats.rows = nloc;
+    stats.nnz = local_nnz;
+    stats.mean = stats.max = stats.min = double(n);
+    lda = (nloc + 15) / 16 * 16;
+    if (lda == 0) lda = 16;
+    d_dense.alloc(size_t(lda) * size_t(std::max<int64_t>(ext_len, 1)) * ss());
+    const char* src = static_cast<const char*>(a);
+    const size_t s = size_t(ss());
+    auto copy_cols = [&](int64_t gcol0, int64_t ncols, int64_t ecol0) {
+        if (ncols <= 0 || nloc <= 0) return;
+        EIGSOL_CUDA(cudaMemcpy2DAsync(d_dense.as<char>() + size_t(ecol0) * size_t(lda) * s, size_t(lda) * s,
+                                      src + (size_t(gcol0) * size_t(lda_host) + size_t(lo)) * s, size_t(lda_host) * s,
+                                      size_t(nloc) * s, size_t(ncols), cudaMemcpyHostToDevice, stream));
+    };
+    copy_cols(lo, nloc, 0);
+    copy_cols(0, lo, nloc_pad);
+    copy_cols(hi, n - hi, nloc_pad + lo);
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    set_kernel(K_GEMV, 0);
+}
+
+// -------------------------------------------------------------------------------------------------
+// Launch configuration: persistent grids sized from the SM count and the kernel's occupancy.
+// -------------------------------------------------------------------------------------------------
+template <class K> static int occupancy(K kern, int block) {
+    int nb = 0;
+    EIGSOL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, block, 0));
+    return std::max(nb, 1);
+}
+
+template <class S> static int sparse_occupancy(int kernel, int lanes) {
+    constexpr int B = 256;
+    switch (kernel) {
+        case K_CSR_SCALAR: return occupancy(spmv_csr_scalar_kernel<S, B>, B);
+        case K_CSR_STREAM: return occupancy(spmv_csr_stream_kernel<S, B>, B);
+        case K_SELL:
+            return lanes == 2 ? occupancy(spmv_sell_kernel<S, 2, B>, B) : occupancy(spmv_sell_kernel<S, 1, B>, B);
+        case K_CSR_VECTOR:
+            switch (lanes) {
+                case 2: return occupancy(spmv_csr_vector_kernel<S, 2, B>, B);
+                case 4: return occupancy(spmv_csr_vector_kernel<S, 4, B>, B);
+                case 8: return occupancy(spmv_csr_vector_kernel<S, 8, B>, B);
+                case 16: return occupancy(spmv_csr_vector_kernel<S, 16, B>, B);
+                default: return occupancy(spmv_csr_vector_kernel<S, 32, B>, B);
+            }
+    }
+    return 1;
+}
+
+void MatrixImpl::configure_launch() {
+    block = 256;
+    const int64_t s = ss();
+    if (dense) {
+        const int RT = block * (dtype ? 1 : 2);
+        ntiles = int(std::max<int64_t>((nloc + RT - 1) / RT, 1));
+        const int target = sm_count * env_int("EIGSOL_B200_GEMV_WAVES", 4);
+        nseg = std::max(1, target / ntiles);
+        nseg = int(std::min<int64_t>(nseg, std::max<int64_t>(1, (ext_len + 31) / 32)));
+        grid = ntiles * nseg;
+        nslots = ntiles;
+        d_dense_partial.alloc(size_t(nseg) * size_t(lda) * size_t(s));
+        d_tile_ticket.alloc(sizeof(unsigned) * size_t(ntiles));
+        stored_bytes = s * lda * ext_len + s * (ext_len + nloc) + 2 * s * int64_t(nseg) * lda;
+    } else {
+        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes) : sparse_occupancy<double>(kernel, lanes);
+        const int resident = sm_count * occ;
+        int64_t need = 1;
+        switch (kernel) {
+            case K_CSR_SCALAR: need = (nloc + block - 1) / block; break;
+            case K_CSR_VECTOR: need = (nloc * lanes + block - 1) / block; break;
+            case K_CSR_STREAM: need = nblk; break;
+            case K_SELL: need = (sell_nslices + (block / 32) - 1) / (block / 32); break;
+        }
+        grid = int(std::max<int64_t>(1, std::min<int64_t>(need, resident)));
+        nslots = grid;
+        const int64_t xz = s * (nloc + nhalo) + s * nloc;
+        if (kernel == K_SELL) stored_bytes = sell_padded * (s + 4) + 8 * (sell_nslices + 1) + xz;
+        else stored_bytes = local_nnz * (s + 4) + 4 * (nloc + 1) + xz + (kernel == K_CSR_STREAM ? 4 * int64_t(nblk + 1) : 0);
+    }
+    d_partials.alloc(sizeof(double) * 3 * size_t(nslots));
+}
+
+// One matvec launch on `stream`.  All launches of a handle are identical (the kernels pick the
+// ping-pong buffer from the device state), which is what lets a CUDA graph of them be replayed.
+template <class S> static void launch_sparse(MatrixImpl& m, int fused) {
+    constexpr int B = 256;
+    IterArgs<S> it{m.buf[0].as<S>(), m.buf[1].as<S>(), m.d_state.as<PowerState>(), m.d_partials.as<double>(), fused};
+    CsrView<S> A{int32_t(m.nloc), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
+    const dim3 g(m.grid), b(B);
+    cudaStream_t st = m.stream;
+    switch (m.kernel) {
+        case K_CSR_SCALAR: spmv_csr_scalar_kernel<S, B><<<g, b, 0, st>>>(A, it); break;
+        case K_CSR_STREAM: spmv_csr_stream_kernel<S, B><<<g, b, 0, st>>>(A, m.d_rowblk.as<int32_t>(), m.nblk, it); break;
+        case K_SELL: {
+            SellView<S> V{int32_t(m.nloc), int32_t(m.sell_nslices), m.d_sell_off.as<int64_t>(), m.d_sell_col.as<int32_t>(),
+                          m.d_sell_val.as<S>()};
+            if (m.lanes == 2) spmv_sell_kernel<S, 2, B><<<g, b, 0, st>>>(V, it);
+            else spmv_sell_kernel<S, 1, B><<<g, b, 0, st>>>(V, it);
+            break;
+        }
+        case K_CSR_VECTOR:
+            switch (m.lanes) {
+                case 2: spmv_csr_vector_kernel<S, 2, B><<<g, b, 0, st>>>(A, it); break;
+                case 4: spmv_csr_vector_kernel<S, 4, B><<<g, b, 0, st>>>(A, it); break;
+                case 8: spmv_csr_vector_kernel<S, 8, B><<<g, b, 0, st>>>(A, it); break;
+                case 16: spmv_csr_vector_kernel<S, 16, B><<<g, b, 0, st>>>(A, it); break;
+                default: spmv_csr_vector_kernel<S, 32, B><<<g, b, 0, st>>>(A, it); break;
+            }
+            break;
+        default: throw StateError("no sparse kernel selected");
+    }
+}
+
+template <class S> static void launch_dense(MatrixImpl& m, int fused) {
+    constexpr int B = 256;
+    IterArgs<S> it{m.buf[0].as<S>(), m.buf[1].as<S>(), m.d_state.as<PowerState>(), m.d_partials.as<double>(), fused};
+    DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
+                   m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
+    gemv_colmajor_kernel<S, B><<<dim3(m.grid), dim3(B), 0, m.stream>>>(A, it);
+}
+
+void MatrixImpl::launch_matvec(int fused) {
+    if (dense) {
+        if (dtype) launch_dense<double2>(*this, fused);
+        else launch_dense<double>(*this, fused);
+    } else {
+        if (dtype) launch_sparse<double2>(*this, fused);
+        else launch_sparse<double>(*this, fused);
+    }
+    ++launches;
+}
+
+// -------------------------------------------------------------------------------------------------
+// The loop.
+// -------------------------------------------------------------------------------------------------
+void MatrixImpl::begin(const void* x0, int max_it, double tol) {
+    if (!x0) throw PlanError("null start vector");
+    EIGSOL_CUDA(cudaSetDevice(device));
+    PowerState st;
+    std::memset(&st, 0, sizeof st);
+    st.q[0] = 1.0;  // x0 arrives normalised (power_method.hpp:62); launch 0 uses it as is
+    st.q[1] = 0.0;
+    st.tol = tol;
+    st.final_q = 1.0;
+    st.max_trips = max_it;
+    st.stop = max_it <= 0 ? STOP_MAX_TRIPS : STOP_NONE;  // the loop of :68 never runs
+    max_trips = max_it;
+    issued = 0;
+    const size_t s = size_t(ss());
+    EIGSOL_CUDA(cudaMemcpyAsync(d_state.p, &st, sizeof st, cudaMemcpyHostToDevice, stream));
+    for (auto& b : buf) EIGSOL_CUDA(cudaMemsetAsync(b.p, 0, size_t(ext_len) * s, stream));
+    if (nloc)
+        EIGSOL_CUDA(cudaMemcpyAsync(buf[0].p, static_cast<const char*>(x0) + size_t(lo) * s, size_t(nloc) * s,
+                                    cudaMemcpyHostToDevice, stream));
+    if (dense) EIGSOL_CUDA(cudaMemsetAsync(d_tile_ticket.p, 0, sizeof(unsigned) * size_t(ntiles), stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));  // x0 is a borrowed host pointer
+    begun = true;
+}
+
+// x exchange of the multi-GPU path: every rank sends the entries its peers' rows reference and
+// receives its own halo (semantically the all-gather of x; only the referenced entries move).
+template <class S> static void exchange_impl(MatrixImpl& m, int in) {
+    S* u = m.buf[in].as<S>();
+    const int ncclT = ncclDouble;
+    const size_t mul = sizeof(S) / sizeof(double);
+    if (m.need_pack) {
+        for (int q = 0; q < m.nranks; ++q) {
+            if (m.send_count[q] == 0 || m.send_contig[q]) continue;
+            const int cnt = int(m.send_count[q]);
+            const int g = std::min((cnt + 255) / 256, m.sm_count * 4);
+            pack_kernel<S><<<g, 256, 0, m.stream>>>(u, m.d_send_idx.as<int32_t>() + m.send_off[q],
+                                                   m.d_sendbuf.as<S>() + m.send_off[q], cnt);
+            ++m.launches;
+        }
+    }
+    EIGSOL_NCCL(nccl().GroupStart());
+    for (int q = 0; q < m.nranks; ++q) {
+        if (q == m.rank) continue;
+        if (m.send_count[q] > 0) {
+            const S* src = m.send_contig[q] ? u + m.send_start[q] : m.d_sendbuf.as<S>() + m.send_off[q];
+            EIGSOL_NCCL(nccl().Send(src, size_t(m.send_count[q]) * mul, ncclT, q, m.comm->nccl_comm, m.stream));
+        }
+        if (m.halo.peer_count[q] > 0)
+            EIGSOL_NCCL(nccl().Recv(u + m.nloc_pad + m.halo.peer_off[q], size_t(m.halo.peer_count[q]) * mul, ncclT, q,
+                                    m.comm->nccl_comm, m.stream));
+    }
+    EIGSOL_NCCL(nccl().GroupEnd());
+}
+
+void MatrixImpl::exchange_halo(int in) {
+    if (nranks == 1) return;
+    if (dtype) exchange_impl<double2>(*this, in);
+    else exchange_impl<double>(*this, in);
+}
+
+void MatrixImpl::issue_trips(int k) {
+    if (k <= 0) return;
+    EIGSOL_CUDA(cudaSetDevice(device));
+    if (nranks == 1) {
+        const int glen = env_int("EIGSOL_B200_GRAPH", 16);
+        if (glen > 1 && k >= glen) {
+            if (!graph || graph_len != glen) {
+                drop_graph();
+                cudaGraph_t g = nullptr;
+                EIGSOL_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+                const int64_t keep = launches;
+                for (int i = 0; i < glen; ++i) launch_matvec(1);
+                launches = keep;
+                EIGSOL_CUDA(cudaStreamEndCapture(stream, &g));
+                EIGSOL_CUDA(cudaGraphInstantiate(&graph, g, 0));
+                cudaGraphDestroy(g);
+                graph_len = glen;
+            }
+            while (k >= glen) {
+                EIGSOL_CUDA(cudaGraphLaunch(graph, stream));
+                launches += glen;
+                issued += glen;
+                k -= glen;
+            }
+        }
+        for (int i = 0; i < k; ++i) {
+            launch_matvec(1);
+            ++issued;
+        }
+        EIGSOL_CUDA(cudaGetLastError());
+        return;
+    }
+    for (int i = 0; i < k; ++i) {
+        exchange_halo(issued & 1);
+        launch_matvec(0);
+        reduce_partials_kernel<256><<<1, 256, 0, stream>>>(d_partials.as<double>(), nslots, d_state.as<PowerState>(),
+                                                          d_scal.as<double>());
+        EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 3, ncclDouble, ncclSum, comm->nccl_comm, stream));
+        finalize_kernel<<<1, 32, 0, stream>>>(d_state.as<PowerState>(), d_scal.as<double>());
+        launches += 2;
+        ++issued;
+    }
+    EIGSOL_CUDA(cudaGetLastError());
+}
+
+const PowerState& MatrixImpl::poll_state() {
+    EIGSOL_CUDA(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(PowerState), cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    return *h_state.as<PowerState>();
+}
+
+void MatrixImpl::step(int trips, float* ms_out) {
+    if (!begun) throw StateError("eigsol_b200_power_step called before eigsol_b200_power_begin");
+    if (trips < 0) throw PlanError("negative trip count");
+    EIGSOL_CUDA(cudaSetDevice(device));
+    EIGSOL_CUDA(cudaEventRecord(ev0, stream));
+    issue_trips(trips);
+    EIGSOL_CUDA(cudaEventRecord(ev1, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    if (ms_out) EIGSOL_CUDA(cudaEventElapsedTime(ms_out, ev0, ev1));
+}
+
+// Local slice on the device -> global vector on the host (every rank gets the full vector).
+void MatrixImpl::gather_download(const void* d_local, void* host_out) {
+    const size_t s = size_t(ss());
+    if (nranks == 1) {
+        if (n) EIGSOL_CUDA(cudaMemcpyAsync(host_out, d_local, size_t(n) * s, cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        return;
+    }
+    const size_t mul = s / sizeof(double);
+    EIGSOL_NCCL(nccl().GroupStart());
+    for (int r = 0; r < nranks; ++r) {
+        const int64_t cnt = row_begin[r + 1] - row_begin[r];
+        if (cnt == 0) continue;
+        EIGSOL_NCCL(nccl().Broadcast(d_local, d_xglob.as<char>() + size_t(row_begin[r]) * s, size_t(cnt) * mul, ncclDouble,
+                                     r, comm->nccl_comm, stream));
+    }
+    EIGSOL_NCCL(nccl().GroupEnd());
+    EIGSOL_CUDA(cudaMemcpyAsync(host_out, d_xglob.p, size_t(n) * s, cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+}
+
+void MatrixImpl::end(void* x_out, double lambda_out[2], int* iters, int* conv) {
+    if (!begun) throw StateError("eigsol_b200_power_end called before eigsol_b200_power_begin");
+    EIGSOL_CUDA(cudaSetDevice(device));
+    const PowerState st = poll_state();
+    if (x_out) {
+        const int g = int(std::max<int64_t>(1, std::min<int64_t>((nloc + 255) / 256, sm_count * 8)));
+        if (dtype)
+            normalize_result_kernel<double2><<<g, 256, 0, stream>>>(buf[0].as<double2>(), buf[1].as<double2>(),
+                                                                   d_state.as<PowerState>(), d_xloc.as<double2>(), int(nloc));
+        else
+            normalize_result_kernel<double><<<g, 256, 0, stream>>>(buf[0].as<double>(), buf[1].as<double>(),
+                                                                  d_state.as<PowerState>(), d_xloc.as<double>(), int(nloc));
+        ++launches;
+        EIGSOL_CUDA(cudaGetLastError());
+        gather_download(d_xloc.p, x_out);
+    }
+    if (lambda_out) {
+        lambda_out[0] = st.lambda[0];
+        lambda_out[1] = st.lambda[1];
+    }
+    if (iters) *iters = st.trips;
+    if (conv) *conv = st.converged;
+}
+
+// Whole solve: power_method.hpp:61-98.  maxIterations trips need maxIterations+1 launches (launch 0
+// is y = A x0 of trip 0; launch l >= 1 closes trip l-1).  The host polls the device state between
+// batches; launches issued past the stopping point are no-ops on the device.
+void MatrixImpl::run(const void* x0, int max_it, double tol, void* x_out, double lambda_out[2], int* iters, int* conv) {
+    begin(x0, max_it, tol);
+    if (max_it > 0) {
+        int64_t remaining = int64_t(max_it) + 1;
+        int batch = env_int("EIGSOL_B200_POLL", 64);
+        if (batch < 1) batch = 1;
+        while (remaining > 0) {
+            const int k = int(std::min<int64_t>(remaining, batch));
+            issue_trips(k);
+            remaining -= k;
+            if (poll_state().stop != STOP_NONE) break;
+        }
+    }
+    end(x_out, lambda_out, iters, conv);
+}
+
+// y = A x alone: launch 0 of the loop with ||x|| taken as 1 leaves A x un-normalised in buffer 1.
+void MatrixImpl::matvec(const void* x, void* y) {
+    begin(x, 1, -1.0);
+    issue_trips(1);
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    gather_download(buf[1].p, y);
+    begun = false;
+}
+
+void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
+    std::memset(info, 0, sizeof *info);
+    info->dtype = dtype;
+    info->is_dense = dense ? 1 : 0;
+    info->n = n;
+    info->nnz = nnz_global;
+    info->local_rows = nloc;
+    info->local_nnz = local_nnz;
+    info->halo = nhalo;
+    info->kernel = kernel;
+    info->lanes_per_row = lanes;
+    info->grid = grid;
+    info->block = block;
+    info->row_len_mean = stats.mean;
+    info->row_len_max = stats.max;
+    info->row_len_cv = stats.cv;
+    const int64_t s = ss();
+    info->alg_bytes = dense ? s * nloc * n + s * (n + nloc)
+                            : local_nnz * (s + 4) + 4 * (nloc + 1) + s * (nloc + nhalo) + s * nloc;
+    info->stored_bytes = stored_bytes;
+    info->nranks = nranks;
+    info->rank = rank;
+    int per_trip = 1;
+    if (nranks > 1) {
+        per_trip += 2;
+        for (int q = 0; q < nranks; ++q)
+            if (send_count[q] > 0 && !send_contig[q]) ++per_trip;
+    }
+    info->kernels_per_trip = per_trip;
+}
+
+}  // namespace eigsol_b200
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+using namespace eigsol_b200;
+
+struct eigsol_b200_matrix {
+    MatrixImpl impl;
+};
+struct eigsol_b200_comm {
+    Comm impl;
+};
+
+namespace {
+std::mutex g_api_mutex;  // calls are serialised (SURVEY.md 8b "Threading")
+
+template <class F> int guarded(F&& f) {
+    try {
+        g_last_error.clear();
+        return f();
+    } catch (const DeviceError& e) {
+        g_last_error = e.what();
+        return EIGSOL_B200_ERR_DEVICE;
+    } catch (const StateError& e) {
+        g_last_error = e.what();
+        return EIGSOL_B200_ERR_STATE;
+    } catch (const PlanError& e) {
+        g_last_error = std::string("eigsol_b200: invalid argument: ") + e.what();
+        return EIGSOL_B200_ERR_INVALID;
+    } catch (const std::bad_alloc&) {
+        g_last_error = "eigsol_b200: out of host memory";
+        return EIGSOL_B200_ERR_INVALID;
+    } catch (const std::exception& e) {
+        g_last_error = std::string("powerMethod: device error: ") + e.what();
+        return EIGSOL_B200_ERR_DEVICE;
+    }
+}
+
+int fail(int code, const char* msg) {
+    g_last_error = msg;
+    return code;
+}
+
+// power_method.hpp:52-58, same order, same messages
+int check_shape(int64_t rows, int64_t cols) {
+    if (rows < 0 || cols < 0) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: negative dimension");
+    if (rows != cols) return fail(EIGSOL_B200_ERR_NOT_SQUARE, "powerMethod: matrix must be square");
+    if (rows == 0) return fail(EIGSOL_B200_ERR_ZERO_SIZE, "powerMethod: matrix has zero size");
+    return EIGSOL_B200_OK;
+}
+int check_dtype(int dtype) {
+    if (dtype != EIGSOL_B200_F64 && dtype != EIGSOL_B200_C128)
+        return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: dtype must be 0 (f64) or 1 (c128)");
+    return EIGSOL_B200_OK;
+}
+}  // namespace
+
+extern "C" {
+
+const char* eigsol_b200_last_error(void) { return g_last_error.c_str(); }
+
+int eigsol_b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char* eigsol_b200_version(void) { return "eigsol_b200 0.1 (sm_100a)"; }
+
+int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                                  const void* values, eigsol_b200_comm* comm, eigsol_b200_matrix** out) {
+    if (!out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null output handle");
+    *out = nullptr;
+    if (int e = check_dtype(dtype)) return e;
+    if (int e = check_shape(rows, cols)) return e;
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        if (!outer || (outer[cols] > 0 && (!inner || !values))) throw PlanError("null CSC array");
+        std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
+        MatrixImpl& m = h->impl;
+        m.init_common(dtype, comm ? &comm->impl : nullptr);
+        m.n = rows;
+        CsrHost g = csc_to_csr(dtype, rows, cols, outer, inner, values);
+        m.row_begin = partition_rows(rows, g.rowptr.data(), m.nranks);
+        if (m.nranks == 1) {
+            m.init_sparse_local(std::move(g));
+        } else {
+            const int64_t lo = m.row_begin[m.rank], hi = m.row_begin[m.rank + 1];
+            CsrHost loc;
+            loc.dtype = dtype;
+            loc.rows = hi - lo;
+            loc.cols = cols;
+            loc.rowptr.resize(size_t(hi - lo) + 1);
+            const int32_t p0 = g.rowptr[lo];
+            for (int64_t i = lo; i <= hi; ++i) loc.rowptr[i - lo] = g.rowptr[i] - p0;
+            loc.colidx.assign(g.colidx.begin() + p0, g.colidx.begin() + g.rowptr[hi]);
+            loc.vals.assign(g.vals.begin() + int64_t(p0) * g.spd(), g.vals.begin() + int64_t(g.rowptr[hi]) * g.spd());
+            g = CsrHost();
+            m.init_sparse_local(std::move(loc));
+        }
+        *out = h.release();
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_matrix_create_csr_rows(int dtype, int64_t n, int64_t row_begin, int64_t row_count, const int32_t* rowptr,
+                                       const int32_t* colidx, const void* values, eigsol_b200_comm* comm,
+                                       eigsol_b200_matrix** out) {
+    if (!out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null output handle");
+    *out = nullptr;
+    if (int e = check_dtype(dtype)) return e;
+    if (int e = check_shape(n, n)) return e;
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        validate_csr_rows(n, row_count, rowptr, colidx);
+        if (rowptr[row_count] > 0 && !values) throw PlanError("null values array");
+        std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
+        MatrixImpl& m = h->impl;
+        m.init_common(dtype, comm ? &comm->impl : nullptr);
+        m.n = n;
+        if (m.nranks == 1) {
+            if (row_begin != 0 || row_count != n) throw PlanError("without a comm the row block must be the whole matrix");
+            m.row_begin = {0, n};
+        } else {
+            const std::vector<int64_t> begins = comm_allgather_i64(m.comm, row_begin);
+            m.row_begin = begins;
+            m.row_begin.push_back(n);
+            for (int r = 0; r < m.nranks; ++r)
+                if (m.row_begin[r] > m.row_begin[r + 1]) throw PlanError("row blocks of the ranks are not ascending");
+            if (m.row_begin[0] != 0 || m.row_begin[m.rank + 1] - m.row_begin[m.rank] != row_count)
+                throw PlanError("row blocks of the ranks do not tile [0, n)");
+        }
+        CsrHost loc;
+        loc.dtype = dtype;
+        loc.rows = row_count;
+        loc.cols = n;
+        loc.rowptr.assign(rowptr, rowptr + row_count + 1);
+        const int64_t nnz = rowptr[row_count];
+        loc.colidx.assign(colidx, colidx + nnz);
+        loc.vals.assign(static_cast<const double*>(values), static_cast<const double*>(values) + nnz * loc.spd());
+        m.init_sparse_local(std::move(loc));
+        *out = h.release();
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_matrix_create_dense(int dtype, int64_t rows, int64_t cols, const void* a, int64_t lda,
+                                    eigsol_b200_comm* comm, eigsol_b200_matrix** out) {
+    if (!out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null output handle");
+    *out = nullptr;
+    if (int e = check_dtype(dtype)) return e;
+    if (int e = check_shape(rows, cols)) return e;
+    if (!a || lda < rows) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: bad dense matrix pointer / lda");
+    if (rows > INT32_MAX / 2) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: dense order too large");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
+        MatrixImpl& m = h->impl;
+        m.init_common(dtype, comm ? &comm->impl : nullptr);
+        m.init_dense(rows, a, lda);
+        *out = h.release();
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_matrix_destroy(eigsol_b200_matrix* m) {
+    if (!m) return EIGSOL_B200_OK;
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        cudaSetDevice(m->impl.device);
+        delete m;
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_matrix_get_info(const eigsol_b200_matrix* m, eigsol_b200_matrix_info* info) {
+    if (!m || !info) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle / info");
+    m->impl.fill_info(info);
+    return EIGSOL_B200_OK;
+}
+
+int eigsol_b200_matrix_set_kernel(eigsol_b200_matrix* m, int kernel, int lanes) {
+    if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        EIGSOL_CUDA(cudaSetDevice(m->impl.device));
+        m->impl.begun = false;
+        m->impl.set_kernel(kernel, lanes);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_power_run(eigsol_b200_matrix* m, const void* x0, int max_iterations, double tolerance, void* x_out,
+                          double lambda_out[2], int* iterations_out, int* converged_out) {
+    if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        m->impl.run(x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_power_begin(eigsol_b200_matrix* m, const void* x0, int max_iterations, double tolerance) {
+    if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        m->impl.begin(x0, max_iterations, tolerance);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_power_step(eigsol_b200_matrix* m, int trips, float* ms_out) {
+    if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        m->impl.step(trips, ms_out);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_power_end(eigsol_b200_matrix* m, void* x_out, double lambda_out[2], int* iterations_out,
+                          int* converged_out) {
+    if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        m->impl.end(x_out, lambda_out, iterations_out, converged_out);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_matvec(eigsol_b200_matrix* m, const void* x, void* y) {
+    if (!m || !x || !y) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        m->impl.matvec(x, y);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int64_t eigsol_b200_matrix_launch_count(const eigsol_b200_matrix* m) { return m ? m->impl.launches : 0; }
+
+}  // extern "C"
+
+// ---- one-shot entry points ------------------------------------------------------------------------
+extern "C" {
+
+int eigsol_b200_power_csc(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                          const void* values, const void* x0, int max_iterations, double tolerance, void* x_out,
+                          double lambda_out[2], int* iterations_out, int* converged_out) {
+    eigsol_b200_matrix* m = nullptr;
+    int e = eigsol_b200_matrix_create_csc(dtype, rows, cols, outer, inner, values, nullptr, &m);
+    if (e) return e;
+    e = eigsol_b200_power_run(m, x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
+    const std::string keep = g_last_error;
+    eigsol_b200_matrix_destroy(m);
+    if (e) g_last_error = keep;
+    return e;
+}
+
+int eigsol_b200_power_dense(int dtype, int64_t rows, int64_t cols, const void* a, int64_t lda, const void* x0,
+                            int max_iterations, double tolerance, void* x_out, double lambda_out[2],
+                            int* iterations_out, int* converged_out) {
+    eigsol_b200_matrix* m = nullptr;
+    int e = eigsol_b200_matrix_create_dense(dtype, rows, cols, a, lda, nullptr, &m);
+    if (e) return e;
+    e = eigsol_b200_power_run(m, x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
+    const std::string keep = g_last_error;
+    eigsol_b200_matrix_destroy(m);
+    if (e) g_last_error = keep;
+    return e;
+}
+
+// ---- multi-GPU group ------------------------------------------------------------------------------
+int eigsol_b200_comm_unique_id(void* id128) {
+    if (!id128) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null id buffer");
+    return guarded([&] {
+        ncclUniqueId id;
+        EIGSOL_NCCL(nccl().GetUniqueId(&id));
+        std::memcpy(id128, &id, sizeof id);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_comm_create(int rank, int nranks, const void* id128, int device, eigsol_b200_comm** out) {
+    if (!out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null output handle");
+    *out = nullptr;
+    if (nranks < 1 || rank < 0 || rank >= nranks || (nranks > 1 && !id128))
+        return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: bad rank / nranks / id");
+    return guarded([&] {
+        require_device();
+        std::unique_ptr<eigsol_b200_comm> h(new eigsol_b200_comm);
+        Comm& c = h->impl;
+        c.rank = rank;
+        c.nranks = nranks;
+        c.device = device;
+        EIGSOL_CUDA(cudaSetDevice(device));
+        EIGSOL_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        c.scratch.alloc(sizeof(int64_t) * size_t(4 * nranks + 16));
+        if (nranks > 1) {
+            ncclUniqueId id;
+            std::memcpy(&id, id128, sizeof id);
+            EIGSOL_NCCL(nccl().CommInitRank(&c.nccl_comm, nranks, id, rank));
+        }
+        *out = h.release();
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_comm_destroy(eigsol_b200_comm* comm) {
+    if (!comm) return EIGSOL_B200_OK;
+    return guarded([&] {
+        cudaSetDevice(comm->impl.device);
+        delete comm;
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_comm_max_float(eigsol_b200_comm* comm, float* inout) {
+    if (!comm || !inout) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    return guarded([&] {
+        Comm& c = comm->impl;
+        if (c.nranks == 1) return int(EIGSOL_B200_OK);
+        EIGSOL_CUDA(cudaSetDevice(c.device));
+        float* d = c.scratch.as<float>();
+        EIGSOL_CUDA(cudaMemcpyAsync(d, inout, sizeof(float), cudaMemcpyHostToDevice, c.stream));
+        EIGSOL_NCCL(nccl().AllReduce(d, d, 1, ncclFloat, ncclMax, c.nccl_comm, c.stream));
+        EIGSOL_CUDA(cudaMemcpyAsync(inout, d, sizeof(float), cudaMemcpyDeviceToHost, c.stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(c.stream));
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+// ---- host-side planning (no GPU) ------------------------------------------------------------------
+int eigsol_b200_csc_to_csr(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                           const void* values, int32_t* rowptr, int32_t* colidx, void* values_out) {
+    if (int e = check_dtype(dtype)) return e;
+    return guarded([&] {
+        validate_csc(rows, cols, outer, inner);
+        if (!rowptr || (outer[cols] > 0 && (!colidx || !values || !values_out))) throw PlanError("null array");
+        csc_to_csr_raw(dtype, rows, cols, outer, inner, static_cast<const double*>(values), rowptr, colidx,
+                       static_cast<double*>(values_out));
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_partition_rows(int64_t rows, const int32_t* rowptr, int nranks, int64_t* row_begin) {
+    return guarded([&] {
+        if (rows < 0 || !rowptr || !row_begin) throw PlanError("null array / negative size");
+        const std::vector<int64_t> rb = partition_rows(rows, rowptr, nranks);
+        std::copy(rb.begin(), rb.end(), row_begin);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_halo_plan(int64_t row_count, const int32_t* rowptr, const int32_t* colidx, int nranks,
+                          const int64_t* row_begin, int rank, int64_t* halo_count, int32_t* halo_cols,
+                          int64_t* peer_count) {
+    return guarded([&] {
+        if (row_count < 0 || !rowptr || !row_begin || !halo_count || nranks < 1 || rank < 0 || rank >= nranks)
+            throw PlanError("bad halo plan arguments");
+        const std::vector<int64_t> rb(row_begin, row_begin + nranks + 1);
+        const HaloPlan h = halo_plan(row_count, rowptr, colidx, rb, rank);
+        *halo_count = int64_t(h.cols.size());
+        if (halo_cols) std::copy(h.cols.begin(), h.cols.end(), halo_cols);
+        if (peer_count) std::copy(h.peer_count.begin(), h.peer_count.end(), peer_count);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_choose_kernel(int dtype, int64_t rows, const int32_t* rowptr, int* kernel_out, int* lanes_out) {
+    if (int e = check_dtype(dtype)) return e;
+    return guarded([&] {
+        if (rows < 0 || !rowptr || !kernel_out || !lanes_out) throw PlanError("null array / negative size");
+        const KernelChoice c = choose_kernel(dtype, row_stats(rows, rowptr));
+        *kernel_out = c.kernel;
+        *lanes_out = c.lanes;
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+}  // extern "C"
+
+// ---- x0 for callers without Eigen -----------------------------------------------------------------
+namespace {
+inline double eigen_style_random_real() {
+    // RandomImpl.h:66-69: fill 52 mantissa bits from 31-bit rand() words, low word first;
+    // :89-99: OR into the bit pattern of 2.0 (-> [2,4)) and subtract 3 (-> [-1,1)).
+    uint64_t bits = 0;
+    for (int shift = 0; shift < 52; shift += 31) bits |= uint64_t(std::rand()) << shift;
+    bits &= (~uint64_t(0)) >> 12;
+    const double two = 2.0;
+    uint64_t tb;
+    std::memcpy(&tb, &two, sizeof tb);
+    bits |= tb;
+    double r;
+    std::memcpy(&r, &bits, sizeof r);
+    return r - 3.0;
+}
+}  // namespace
+
+extern "C" int eigsol_b200_random_unit(int dtype, int64_t n, int seed, void* x_out) {
+    if (int e = check_dtype(dtype)) return e;
+    if (n < 0 || (n > 0 && !x_out)) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: bad vector");
+    if (seed >= 0) std::srand(unsigned(seed));
+    double* x = static_cast<double*>(x_out);
+    if (dtype == EIGSOL_B200_F64) {
+        for (int64_t i = 0; i < n; ++i) x[i] = eigen_style_random_real();
+    } else {
+        for (int64_t i = 0; i < n; ++i) {
+            const double im = eigen_style_random_real();
+            const double re = eigen_style_random_real();
+            x[2 * i] = re;
+            x[2 * i + 1] = im;
+        }
+    }
+    const int64_t nd = dtype ? 2 * n : n;
+    double z = 0.0;
+    for (int64_t i = 0; i < nd; ++i) z += x[i] * x[i];
+    if (z > 0.0) {
+        const double nrm = std::sqrt(z);
+        for (int64_t i = 0; i < nd; ++i) x[i] /= nrm;
+    }
+    return EIGSOL_B200_OK;
+}

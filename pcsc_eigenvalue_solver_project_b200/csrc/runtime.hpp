@@ -1,0 +1,149 @@
+// runtime.hpp -- small host-runtime pieces shared by engine.cu: error plumbing, RAII device memory,
+// and a lazily dlopen()ed NCCL (so a single-GPU caller never needs libnccl to be loadable, and a
+// process that already carries torch's bundled NCCL reuses that copy instead of loading a second one).
+#pragma once
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+namespace eigsol_b200 {
+
+// CUDA / NCCL failures surface as "powerMethod: device error: ..." (SURVEY.md 8b error conventions;
+// the reference itself only throws std::runtime_error, src/power_method/power_method.hpp:54,57,138).
+struct DeviceError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+struct StateError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+inline void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
+    if (e != cudaSuccess) {
+        char buf[512];
+        std::snprintf(buf, sizeof buf, "powerMethod: device error: %s failed: %s (%s:%d)", what,
+                      cudaGetErrorString(e), file, line);
+        throw DeviceError(buf);
+    }
+}
+#define EIGSOL_CUDA(call) ::eigsol_b200::cuda_check((call), #call, __FILE__, __LINE__)
+
+// ---- RAII device / pinned memory ---------------------------------------------------------------
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) {
+            release();
+            p = o.p;
+            bytes = o.bytes;
+            o.p = nullptr;
+            o.bytes = 0;
+        }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    // pad: extra zeroed bytes behind the payload so vector loads may over-read safely
+    void alloc(size_t n, size_t pad = 64) {
+        release();
+        bytes = n;
+        EIGSOL_CUDA(cudaMalloc(&p, n + pad));
+        EIGSOL_CUDA(cudaMemset(p, 0, n + pad));
+    }
+    void upload(const void* src, size_t n, cudaStream_t s) {
+        if (n) EIGSOL_CUDA(cudaMemcpyAsync(p, src, n, cudaMemcpyHostToDevice, s));
+    }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct PinnedBuf {
+    void* p = nullptr;
+    PinnedBuf() = default;
+    PinnedBuf(const PinnedBuf&) = delete;
+    PinnedBuf& operator=(const PinnedBuf&) = delete;
+    ~PinnedBuf() {
+        if (p) cudaFreeHost(p);
+    }
+    void alloc(size_t n) {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        EIGSOL_CUDA(cudaMallocHost(&p, n));
+    }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+// ---- NCCL, loaded on first use -----------------------------------------------------------------
+// Only the handful of entry points this path needs; signatures as in nccl.h 2.27 (ABI-stable).
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { ncclSuccess = 0 };
+enum { ncclInt8 = 0, ncclChar = 0, ncclUint8 = 1, ncclInt32 = 2, ncclInt = 2, ncclUint32 = 3, ncclInt64 = 4,
+       ncclUint64 = 5, ncclFloat16 = 6, ncclFloat32 = 7, ncclFloat = 7, ncclFloat64 = 8, ncclDouble = 8 };
+enum { ncclSum = 0, ncclProd = 1, ncclMax = 2, ncclMin = 3 };
+
+struct NcclApi {
+    int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    void* lib = nullptr;
+};
+
+inline NcclApi& nccl() {
+    static NcclApi api = [] {
+        NcclApi a;
+        // prefer a copy that is already in the process (torch's bundled NCCL), else the system one
+        a.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+        if (!a.lib) a.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!a.lib) a.lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!a.lib) return a;
+        auto sym = [&](const char* n) { return dlsym(a.lib, n); };
+        a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(sym("ncclGetUniqueId"));
+        a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(sym("ncclCommInitRank"));
+        a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(sym("ncclCommDestroy"));
+        a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
+        a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
+        a.AllGather = reinterpret_cast<decltype(a.AllGather)>(sym("ncclAllGather"));
+        a.Broadcast = reinterpret_cast<decltype(a.Broadcast)>(sym("ncclBroadcast"));
+        a.Send = reinterpret_cast<decltype(a.Send)>(sym("ncclSend"));
+        a.Recv = reinterpret_cast<decltype(a.Recv)>(sym("ncclRecv"));
+        a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(sym("ncclGroupStart"));
+        a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(sym("ncclGroupEnd"));
+        return a;
+    }();
+    if (!api.lib || !api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.Send || !api.Recv ||
+        !api.GroupStart || !api.GroupEnd || !api.Broadcast)
+        throw DeviceError("powerMethod: device error: NCCL (libnccl.so.2) could not be loaded");
+    return api;
+}
+
+inline void nccl_check(int r, const char* what, const char* file, int line) {
+    if (r != ncclSuccess) {
+        char buf[512];
+        const char* msg = nccl().GetErrorString ? nccl().GetErrorString(r) : "?";
+        std::snprintf(buf, sizeof buf, "powerMethod: device error: %s failed: %s (%s:%d)", what, msg, file, line);
+        throw DeviceError(buf);
+    }
+}
+#define EIGSOL_NCCL(call) ::eigsol_b200::nccl_check((call), #call, __FILE__, __LINE__)
+
+}  // namespace eigsol_b200
