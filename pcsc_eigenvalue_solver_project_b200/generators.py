@@ -160,3 +160,29 @@ def random_sparse_csr(n: int, mean_row: float, seed: int = 0, complex_values: bo
     if diag_boost and lens[0] > 0:
         vals[0] = diag_boost
     return rowptr.astype(np.int32), colidx, vals
+
+
+def banded_random_csr(n: int, mean_row: float, band: int, seed: int = 0, regular: bool = False):
+    """Large synthetic test matrix for tuning the kernel dispatch (vectorised, no Python row loop).
+    regular=True : every row has k = int(mean_row) entries at the same k sorted offsets inside the band
+                   (a k-point stencil, clipped at the borders);
+    regular=False: row lengths ~ Poisson(mean_row), columns uniform in [r-band, r+band] (duplicates are
+                   allowed: a CSR row may hold the same column twice, the products simply add)."""
+    rng = np.random.default_rng(seed)
+    if regular:
+        k = int(mean_row)
+        offs = np.sort(rng.choice(np.arange(-band, band + 1), size=k, replace=False))
+        rows = np.arange(n, dtype=np.int64)
+        valid = [(rows + o >= 0) & (rows + o < n) for o in offs]
+        vals = [rng.random(n) * 2 - 1 for _ in offs]
+        return _stencil_rows(list(offs), valid, 1.0, vals, 0, n, np.float64)
+    lens = rng.poisson(mean_row, n).astype(np.int64)
+    rowptr = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(lens, out=rowptr[1:])
+    total = int(rowptr[-1])
+    row_of = np.repeat(np.arange(n, dtype=np.int64), lens)
+    cols = np.clip(row_of + rng.integers(-band, band + 1, total), 0, n - 1)
+    order = np.argsort(row_of * n + cols, kind="stable")
+    cols = cols[order].astype(np.int32)
+    vals = rng.random(total) * 2 - 1
+    return rowptr.astype(np.int32), cols, vals

@@ -1,0 +1,211 @@
+"""Host-side logic through the C ABI, no GPU: library exports, CSC->CSR, partition, halo plan,
+kernel choice, x0 generation, argument checking, and the loud failure without a device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+import _golden
+import pcsc_eigenvalue_solver_project_b200 as es
+from pcsc_eigenvalue_solver_project_b200 import _capi
+from pcsc_eigenvalue_solver_project_b200 import generators as gen
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, "include", "eigsol_b200.h")).read()
+    declared = sorted(set(re.findall(r"EIGSOL_B200_API\s+[\w\s\*]+?\b(eigsol_b200_\w+)\s*\(", header)))
+    assert declared, "no declarations parsed"
+    assert sorted(_capi.EXPORTS) == declared  # the ctypes table covers the header exactly
+    L = C.CDLL(_capi.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), f"{name} not exported"
+    assert b"sm_100a" in _capi.lib().eigsol_b200_version()
+
+
+def test_library_is_sm100a_only():
+    import subprocess
+    out = subprocess.run(["cuobjdump", "--list-elf", _capi.LIB_PATH], capture_output=True, text=True).stdout
+    if not out:
+        pytest.skip("cuobjdump unavailable")
+    assert "sm_100a" in out and not re.search(r"sm_(?!100a)\d+", out)
+
+
+def csr_to_csc_arrays(n, rp, ci, v):
+    a = sp.csr_matrix((v, ci, rp), shape=(n, n)).tocsc()
+    a.sort_indices()
+    return a.indptr.astype(np.int32), a.indices.astype(np.int32), np.ascontiguousarray(a.data)
+
+
+@pytest.mark.parametrize("cplx", [False, True])
+def test_csc_to_csr_matches_scipy_and_keeps_column_order(cplx):
+    n = 500
+    rp, ci, v = gen.random_sparse_csr(n, 5.0, seed=3, complex_values=cplx, skew=30.0)
+    outer, inner, cv = csr_to_csc_arrays(n, rp, ci, v)
+    rowptr = np.empty(n + 1, dtype=np.int32)
+    colidx = np.empty(cv.size, dtype=np.int32)
+    vals = np.empty(cv.size, dtype=cv.dtype)
+    _capi.check(_capi.lib().eigsol_b200_csc_to_csr(_capi.dtype_code(cv.dtype), n, n, _capi.ptr(outer), _capi.ptr(inner),
+                                                   _capi.ptr(cv), _capi.ptr(rowptr), _capi.ptr(colidx), _capi.ptr(vals)))
+    assert np.array_equal(rowptr, rp) and np.array_equal(colidx, ci) and np.array_equal(vals, v)
+
+
+def test_csc_to_csr_rejects_malformed():
+    outer = np.array([0, 2, 1], dtype=np.int32)
+    inner = np.array([0, 1], dtype=np.int32)
+    v = np.zeros(2)
+    out = np.zeros(3, dtype=np.int32)
+    with pytest.raises(ValueError, match="not monotone"):
+        _capi.check(_capi.lib().eigsol_b200_csc_to_csr(0, 2, 2, _capi.ptr(outer), _capi.ptr(inner), _capi.ptr(v),
+                                                       _capi.ptr(out), _capi.ptr(out), _capi.ptr(v)))
+    outer = np.array([0, 1, 2], dtype=np.int32)
+    inner = np.array([0, 5], dtype=np.int32)
+    with pytest.raises(ValueError, match="out of range"):
+        _capi.check(_capi.lib().eigsol_b200_csc_to_csr(0, 2, 2, _capi.ptr(outer), _capi.ptr(inner), _capi.ptr(v),
+                                                       _capi.ptr(out), _capi.ptr(out), _capi.ptr(v)))
+
+
+def partition(rp, nranks):
+    rb = np.zeros(nranks + 1, dtype=np.int64)
+    _capi.check(_capi.lib().eigsol_b200_partition_rows(rp.size - 1, _capi.ptr(rp), nranks, _capi.ptr(rb)))
+    return rb
+
+
+def halo(rp_loc, ci_loc, rb, rank):
+    nranks = rb.size - 1
+    cnt = C.c_int64(0)
+    peers = np.zeros(nranks, dtype=np.int64)
+    L = _capi.lib()
+    _capi.check(L.eigsol_b200_halo_plan(rp_loc.size - 1, _capi.ptr(rp_loc), _capi.ptr(ci_loc), nranks, _capi.ptr(rb), rank,
+                                        C.byref(cnt), None, None))
+    cols = np.zeros(max(cnt.value, 1), dtype=np.int32)
+    _capi.check(L.eigsol_b200_halo_plan(rp_loc.size - 1, _capi.ptr(rp_loc), _capi.ptr(ci_loc), nranks, _capi.ptr(rb), rank,
+                                        C.byref(cnt), _capi.ptr(cols), _capi.ptr(peers)))
+    return cols[:cnt.value], peers
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 4, 8])
+def test_partition_balances_nnz_and_tiles_rows(nranks):
+    rp, ci, v = gen.random_sparse_csr(4000, 7.0, seed=5, skew=50.0)
+    rb = partition(rp, nranks)
+    assert rb[0] == 0 and rb[-1] == 4000 and np.all(np.diff(rb) >= 0)
+    per = np.array([rp[rb[p + 1]] - rp[rb[p]] for p in range(nranks)])
+    assert per.sum() == rp[-1]
+    assert per.max() <= rp[-1] / nranks + np.diff(rp).max()  # within one row of the ideal share
+
+
+def test_halo_of_3d_laplacian_slabs_is_two_planes():
+    g = 16
+    rp, ci, v = gen.laplacian_3d(g)
+    rb = partition(rp, 4)
+    for rank in range(4):
+        lo, hi = rb[rank], rb[rank + 1]
+        rpl = (rp[lo:hi + 1] - rp[lo]).astype(np.int32)
+        cil = np.ascontiguousarray(ci[rp[lo]:rp[hi]])
+        cols, peers = halo(rpl, cil, rb, rank)
+        want = np.unique(cil[(cil < lo) | (cil >= hi)])
+        assert np.array_equal(cols, want)
+        assert peers[rank] == 0 and peers.sum() == cols.size
+        nb = [p for p in (rank - 1, rank + 1) if 0 <= p < 4]
+        assert all(peers[p] == g * g for p in nb) and cols.size == g * g * len(nb)
+
+
+def test_kernel_choice_from_row_statistics():
+    def choose(rp, code=0):
+        k, l = C.c_int(0), C.c_int(0)
+        _capi.check(_capi.lib().eigsol_b200_choose_kernel(code, rp.size - 1, _capi.ptr(rp), C.byref(k), C.byref(l)))
+        return k.value, l.value
+    rp, _, _ = gen.laplacian_3d(12)
+    assert choose(rp) == (es.KERNEL_SELL, 2)
+    assert choose(rp, 1) == (es.KERNEL_SELL, 1)
+    rp, _, _ = gen.random_sparse_csr(3000, 6.0, seed=1, skew=60.0)
+    assert choose(rp)[0] == es.KERNEL_CSR_STREAM
+    rp = (np.arange(201) * 300).astype(np.int32)  # 200 rows of 300 entries
+    assert choose(rp) == (es.KERNEL_SELL, 2) or choose(rp)[0] == es.KERNEL_CSR_VECTOR
+    lens = np.random.default_rng(0).integers(100, 900, 500)
+    rp = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    assert choose(rp) == (es.KERNEL_CSR_VECTOR, 32)
+
+
+def test_random_unit_matches_reference_golden():
+    cases, _ = _golden.load()
+    for c in cases:
+        x0 = es.random_unit(c.n, c.dtype, seed=c.seed)
+        assert np.max(np.abs(x0 - c.x0)) <= 4 * np.finfo(float).eps
+    es.srand(77)
+    a = es.random_unit(6)
+    b = es.random_unit(6)
+    es.srand(77)
+    assert np.array_equal(a, es.random_unit(6)) and not np.array_equal(a, b)  # continues the rand() stream
+
+
+def test_api_checks_and_their_order():
+    # scalar mismatch -> square -> zero size, all before any device work (power_method.hpp:137-139,52-58)
+    with pytest.raises(RuntimeError, match="^powerMethod: scalar type mismatch$"):
+        es.powerMethod(es.Matrix(np.zeros((2, 3))), scalar=np.complex128)
+    with pytest.raises(RuntimeError, match="^powerMethod: matrix must be square$"):
+        es.powerMethod(es.Matrix(np.zeros((2, 3))))
+    with pytest.raises(RuntimeError, match="^powerMethod: matrix has zero size$"):
+        es.powerMethod(es.Matrix(np.zeros((0, 0))))
+    es.srand(5)
+    first = es.random_unit(3)
+    es.srand(5)
+    with pytest.raises(RuntimeError):
+        es.powerMethod(es.Matrix(np.zeros((2, 3))))
+    assert np.array_equal(first, es.random_unit(3))  # the throwing call consumed no rand() values
+    # C ABI status codes for the same conditions
+    L = _capi.lib()
+    z = np.zeros(6)
+    lam = np.zeros(2)
+    it, cv = C.c_int(), C.c_int()
+    st = L.eigsol_b200_power_dense(0, 2, 3, _capi.ptr(z), 2, _capi.ptr(z), 5, 1e-10, _capi.ptr(z), _capi.ptr(lam),
+                                   C.byref(it), C.byref(cv))
+    assert st == _capi.ERR_NOT_SQUARE and _capi.last_error() == "powerMethod: matrix must be square"
+    st = L.eigsol_b200_power_dense(0, 0, 0, _capi.ptr(z), 1, _capi.ptr(z), 5, 1e-10, _capi.ptr(z), _capi.ptr(lam),
+                                   C.byref(it), C.byref(cv))
+    assert st == _capi.ERR_ZERO_SIZE and _capi.last_error() == "powerMethod: matrix has zero size"
+    st = L.eigsol_b200_power_dense(7, 2, 2, _capi.ptr(z), 2, _capi.ptr(z), 5, 1e-10, _capi.ptr(z), _capi.ptr(lam),
+                                   C.byref(it), C.byref(cv))
+    assert st == _capi.ERR_INVALID
+
+
+def test_matrix_wrapper_contract():
+    # test/matrix_wrapper_test.cpp:15-114 restated for the Python mirror
+    import copy
+    d = es.Matrix(np.array([[1.0, 2.0], [3.0, 4.0]]))
+    assert d.isDense() and d.scalar_type() is np.float64 and d.type() == ("dense", np.float64)
+    assert d.cast("dense", np.float64)[1, 0] == 3.0 and d.cast("dense", np.float64).flags.f_contiguous
+    s = es.Matrix(sp.csr_matrix(np.array([[0, 1 + 2j], [0, 3.0]])))
+    assert not s.isDense() and s.scalar_type() is np.complex128
+    outer, inner, vals = s.cast("sparse", np.complex128)
+    assert outer.dtype == np.int32 and inner.dtype == np.int32 and list(outer) == [0, 0, 2]
+    v = es.Matrix(np.arange(6.0), 2, 3)  # row-major vector ctor
+    assert v.cast("dense", np.float64)[1, 0] == 3.0
+    with pytest.raises(TypeError):
+        d.cast("sparse", np.float64)
+    with pytest.raises(TypeError):
+        d.cast("dense", np.complex128)
+    with pytest.raises(TypeError):
+        copy.copy(d)
+    with pytest.raises(TypeError):
+        es.Matrix(np.zeros((2, 2), dtype=np.float32))  # outside the B200 path's scalar set
+
+
+def test_no_cpu_fallback_without_device():
+    if es.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(es.EigsolB200Error, match="powerMethod: device error: no CUDA device"):
+        es.powerMethod(es.Matrix(np.eye(2)))
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "pcsc_eigenvalue_solver_project_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "libeigsol_oracle" not in text and "oracle/" not in text.replace("oracle/ ", ""), f

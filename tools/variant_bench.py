@@ -15,7 +15,8 @@ import pcsc_eigenvalue_solver_project_b200 as es
 from pcsc_eigenvalue_solver_project_b200 import generators as gen
 
 VARIANTS = [(es.KERNEL_SELL, 2), (es.KERNEL_SELL, 1), (es.KERNEL_CSR_STREAM, 0), (es.KERNEL_CSR_SCALAR, 0),
-            (es.KERNEL_CSR_VECTOR, 2), (es.KERNEL_CSR_VECTOR, 4), (es.KERNEL_CSR_VECTOR, 8)]
+            (es.KERNEL_CSR_VECTOR, 2), (es.KERNEL_CSR_VECTOR, 4), (es.KERNEL_CSR_VECTOR, 8),
+            (es.KERNEL_CSR_VECTOR, 16), (es.KERNEL_CSR_VECTOR, 32)]
 
 
 def build(cfg):
@@ -42,6 +43,12 @@ def build(cfg):
         n = 8192
         a = gen.dense_random_symmetric(n)
         dm = es.DeviceMatrix.from_matrix(es.Matrix(a))
+        dt = np.float64
+    elif cfg[0] in "si" and cfg[1:].isdigit():
+        # s<k>: regular k-point stencil rows; i<k>: irregular rows, Poisson(k) entries (dispatch tuning)
+        n = 1 << 20
+        rp, ci, v = gen.banded_random_csr(n, int(cfg[1:]), 4096, seed=1, regular=cfg[0] == "s")
+        dm = es.DeviceMatrix.from_csr_rows(n, 0, rp, ci, v)
         dt = np.float64
     else:
         raise SystemExit(f"unknown config {cfg}")
