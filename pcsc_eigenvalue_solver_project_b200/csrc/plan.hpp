@@ -153,17 +153,24 @@ struct KernelChoice {
     int lanes = 0;  // CSR_VECTOR: lanes per row; SELL: rows per lane
 };
 
-// The dispatch rule (DESIGN.md "kernel choice"):
-//   short, regular rows (stencils)      -> SELL: slice padding <= 12.5 %, mean <= 64
-//   short, irregular rows               -> CSR_STREAM (coalesced nnz stream, rows reduced in smem)
-//   medium / long rows                  -> CSR_VECTOR with lanes = pow2 >= mean/2 clipped to [2, 32]
+// The dispatch rule (DESIGN.md "kernel choice"; thresholds from profiles/r01_variants*.jsonl, B200):
+//   very short rows, no long outliers   -> CSR_SCALAR: thread per row straight off the CSR arrays
+//                                          (2D/3D stencils: 98 % of the measured copy bandwidth)
+//   short / medium rows, padding <= 2.5x -> SELL (R = 2 rows per lane for f64, 1 for c128): every
+//                                          stream coalesced; wins from ~8 to 64 entries per row
+//   short rows with long outliers        -> CSR_STREAM (long rows reduced by a whole CTA)
+//   long rows                            -> CSR_VECTOR, lanes = pow2 <= mean clipped to [2, 32]
 inline KernelChoice choose_kernel(int dtype, const RowStats& s) {
     KernelChoice c;
     if (s.rows == 0 || s.nnz == 0) {
         c.kernel = K_CSR_SCALAR;
         return c;
     }
-    if (s.mean <= 64.0 && s.sell_fill <= 1.125) {
+    if (s.mean <= 8.0 && s.max <= 32.0) {
+        c.kernel = K_CSR_SCALAR;
+        return c;
+    }
+    if (s.mean <= 64.0 && s.sell_fill <= 2.5) {
         c.kernel = K_SELL;
         c.lanes = dtype ? 1 : 2;
         return c;

@@ -1,0 +1,133 @@
+#pragma once
+// Drop-in for the reference's src/power_method/power_method.hpp -- same entry points, same checks in
+// the same order, same exceptions and messages, same start vector; the LOOP (reference :61-98) is
+// replaced by one call through the C ABI of libeigsol_b200.so (include/eigsol_b200.h) into the
+// hand-written sm_100a kernels.  There is no host fallback: if the library cannot reach a B200 the
+// call throws std::runtime_error("powerMethod: device error: ...").
+//
+//   powerMethodImpl<Mat>(A, opts)      reference :47-99    (Mat = an Eigen dense or sparse matrix type)
+//   powerMethod<Scalar>(M, opts = {})  reference :135-148  (M = EigSol::Matrix)
+//
+// What stays on the host, exactly as in the reference:
+//   * n != cols  -> "powerMethod: matrix must be square"  (:52-55), then
+//     n == 0     -> "powerMethod: matrix has zero size"   (:56-58), both BEFORE any rand() is consumed;
+//   * x0 = Vector<Scalar>::Random(n); x0.normalize();     (:62) -- the same Eigen expression, hence the
+//     same std::rand() stream and bit-identical start vector;
+//   * powerMethod: "powerMethod: scalar type mismatch"    (:137-139), then the dense/sparse dispatch.
+// Device scalars are double and std::complex<double>; other ScalarConcept types have no device type and
+// throw "powerMethod: scalar type not supported on the B200 path" (after the shape checks).
+//
+// powerMethod(M, ...) keeps M's device-resident copy alive in M (a Matrix cannot move), so repeated
+// solves on the same Matrix upload and transpose only once.
+#include <Eigen/Dense>
+#include <Eigen/Sparse>
+
+#include <cmath>
+#include <complex>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+
+#include "../core/tolerance.hpp"
+#include "../core/types.hpp"
+#include "../matrix/matrix.hpp"
+#include "../option/solver_option.hpp"
+#include "../result/eigen_result.hpp"
+#include "eigsol_b200.h"
+
+namespace EigSol {
+namespace b200_detail {
+
+template <typename S>
+inline constexpr int dtype_code = -1;
+template <>
+inline constexpr int dtype_code<double> = EIGSOL_B200_F64;
+template <>
+inline constexpr int dtype_code<std::complex<double>> = EIGSOL_B200_C128;
+
+template <typename Mat>
+inline constexpr bool is_sparse_v = std::is_base_of_v<Eigen::SparseMatrixBase<Mat>, Mat>;
+
+[[noreturn]] inline void raise_last_error() { throw std::runtime_error(eigsol_b200_last_error()); }
+
+inline void check(int status) {
+    if (status != EIGSOL_B200_OK) raise_last_error();
+}
+
+// Uploads A once; the returned handle owns the device copy.
+template <typename Mat>
+std::shared_ptr<void> upload(const Mat& A) {
+    using Scalar = typename Mat::Scalar;
+    eigsol_b200_matrix* h = nullptr;
+    if constexpr (is_sparse_v<Mat>) {
+        using Canon = Eigen::SparseMatrix<Scalar, Eigen::ColMajor, int>;
+        Canon tmp;
+        const Canon* csc = nullptr;
+        if constexpr (std::is_same_v<Mat, Canon>) {
+            if (A.isCompressed()) csc = &A;
+        }
+        if (!csc) {
+            tmp = A;
+            tmp.makeCompressed();
+            csc = &tmp;
+        }
+        check(eigsol_b200_matrix_create_csc(dtype_code<Scalar>, csc->rows(), csc->cols(), csc->outerIndexPtr(),
+                                            csc->innerIndexPtr(), csc->valuePtr(), nullptr, &h));
+    } else {
+        using Canon = Eigen::Matrix<Scalar, Eigen::Dynamic, Eigen::Dynamic>;
+        if constexpr (std::is_same_v<Mat, Canon>) {
+            check(eigsol_b200_matrix_create_dense(dtype_code<Scalar>, A.rows(), A.cols(), A.data(), A.outerStride(),
+                                                  nullptr, &h));
+        } else {
+            const Canon tmp(A);
+            check(eigsol_b200_matrix_create_dense(dtype_code<Scalar>, tmp.rows(), tmp.cols(), tmp.data(),
+                                                  tmp.outerStride(), nullptr, &h));
+        }
+    }
+    return std::shared_ptr<void>(h, [](void* p) { eigsol_b200_matrix_destroy(static_cast<eigsol_b200_matrix*>(p)); });
+}
+
+// Shape checks + x0 exactly as the reference (:52-62), then the device loop on `slot`'s matrix
+// (uploaded on demand).
+template <typename Mat>
+EigenResult<typename Mat::Scalar> solve(const Mat& A, const SolverOptions& opts, std::shared_ptr<void>& slot) {
+    using Scalar = typename Mat::Scalar;
+    const auto n = A.rows();
+    if (n != A.cols()) throw std::runtime_error("powerMethod: matrix must be square");
+    if (n == 0) throw std::runtime_error("powerMethod: matrix has zero size");
+    if constexpr (dtype_code<Scalar> < 0) {
+        throw std::runtime_error("powerMethod: scalar type not supported on the B200 path");
+    } else {
+        Vector<Scalar> x0 = Vector<Scalar>::Random(n);
+        x0.normalize();
+        if (!slot) slot = upload(A);
+        Vector<Scalar> x(n);
+        double lambda[2] = {0.0, 0.0};
+        int iterations = 0, converged = 0;
+        check(eigsol_b200_power_run(static_cast<eigsol_b200_matrix*>(slot.get()), x0.data(), opts.maxIterations,
+                                    opts.tolerance, x.data(), lambda, &iterations, &converged));
+        Scalar value;
+        if constexpr (std::is_same_v<Scalar, double>) value = lambda[0];
+        else value = Scalar(lambda[0], lambda[1]);
+        return EigenResult<Scalar>(value, x, iterations, converged != 0);
+    }
+}
+
+}  // namespace b200_detail
+
+template <typename Mat>
+    requires ScalarConcept<typename Mat::Scalar>
+EigenResult<typename Mat::Scalar> powerMethodImpl(const Mat& A, const SolverOptions& opts) {
+    std::shared_ptr<void> one_shot;  // device copy lives for this call only
+    return b200_detail::solve(A, opts, one_shot);
+}
+
+template <ScalarConcept Scalar>
+EigenResult<Scalar> powerMethod(const Matrix& M, const SolverOptions& opts = SolverOptions{}) {
+    if (M.scalar_type() != typeid(Scalar)) throw std::runtime_error("powerMethod: scalar type mismatch");
+    if (M.isDense()) return b200_detail::solve(M.cast<Matrix::Dense<Scalar>>(), opts, M.device_slot());
+    return b200_detail::solve(M.cast<Matrix::Sparse<Scalar>>(), opts, M.device_slot());
+}
+
+}  // namespace EigSol

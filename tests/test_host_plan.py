@@ -120,8 +120,12 @@ def test_kernel_choice_from_row_statistics():
         _capi.check(_capi.lib().eigsol_b200_choose_kernel(code, rp.size - 1, _capi.ptr(rp), C.byref(k), C.byref(l)))
         return k.value, l.value
     rp, _, _ = gen.laplacian_3d(12)
+    assert choose(rp) == (es.KERNEL_CSR_SCALAR, 0)  # short regular rows: thread per row
+    rp, _, _ = gen.banded_random_csr(4096, 16, 64, seed=1, regular=True)
     assert choose(rp) == (es.KERNEL_SELL, 2)
     assert choose(rp, 1) == (es.KERNEL_SELL, 1)
+    rp, _, _ = gen.banded_random_csr(4096, 20, 64, seed=1)
+    assert choose(rp) == (es.KERNEL_SELL, 2)        # irregular but bounded padding
     rp, _, _ = gen.random_sparse_csr(3000, 6.0, seed=1, skew=60.0)
     assert choose(rp)[0] == es.KERNEL_CSR_STREAM
     rp = (np.arange(201) * 300).astype(np.int32)  # 200 rows of 300 entries
