@@ -60,7 +60,10 @@ struct DevBuf {
         release();
         bytes = n;
         EIGSOL_CUDA(cudaMalloc(&p, n + pad));
+        // cudaMemset runs on the legacy stream and is asynchronous for device memory, while uploads go
+        // to non-blocking streams: without this synchronisation the zero fill may land AFTER an upload.
         EIGSOL_CUDA(cudaMemset(p, 0, n + pad));
+        EIGSOL_CUDA(cudaDeviceSynchronize());
     }
     void upload(const void* src, size_t n, cudaStream_t s) {
         if (n) EIGSOL_CUDA(cudaMemcpyAsync(p, src, n, cudaMemcpyHostToDevice, s));
