@@ -91,7 +91,8 @@ typedef struct eigsol_b200_matrix_info {
     int32_t nranks;
     int32_t rank;
     int32_t kernels_per_trip; /* kernel launches one power iteration issues on this rank              */
-    int32_t reserved;
+    int32_t exchange;         /* 0 = one GPU (fused finish), 1 = NCCL send/recv + all-reduce,
+                                 2 = peer memory: one kernel does matvec + x exchange + scalar all-reduce */
 } eigsol_b200_matrix_info;
 
 /* ---- diagnostics ------------------------------------------------------------------------------ */

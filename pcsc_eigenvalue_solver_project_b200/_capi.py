@@ -41,11 +41,11 @@ class MatrixInfo(C.Structure):
         ("kernel", C.c_int32), ("lanes_per_row", C.c_int32), ("grid", C.c_int32), ("block", C.c_int32),
         ("row_len_mean", C.c_double), ("row_len_max", C.c_double), ("row_len_cv", C.c_double),
         ("alg_bytes", C.c_int64), ("stored_bytes", C.c_int64),
-        ("nranks", C.c_int32), ("rank", C.c_int32), ("kernels_per_trip", C.c_int32), ("reserved", C.c_int32),
+        ("nranks", C.c_int32), ("rank", C.c_int32), ("kernels_per_trip", C.c_int32), ("exchange", C.c_int32),
     ]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        d = {k: getattr(self, k) for k, _ in self._fields_ }
         d["kernel_name"] = KERNEL_NAMES.get(self.kernel, "?")
         return d
 

@@ -71,6 +71,33 @@ static std::vector<int64_t> comm_allgather_i64(Comm* c, int64_t v) {
     return out;
 }
 
+// all-gather of a fixed-size blob per rank (setup only): out[r * bytes ...] = rank r's blob
+static std::vector<char> comm_allgather_bytes(Comm* c, const void* mine, size_t bytes) {
+    std::vector<char> out(bytes * size_t(c->nranks));
+    DevBuf d;
+    d.alloc(out.size());
+    EIGSOL_CUDA(cudaMemcpyAsync(d.as<char>() + bytes * c->rank, mine, bytes, cudaMemcpyHostToDevice, c->stream));
+    EIGSOL_NCCL(nccl().GroupStart());
+    for (int r = 0; r < c->nranks; ++r)
+        EIGSOL_NCCL(nccl().Broadcast(d.as<char>() + bytes * r, d.as<char>() + bytes * r, bytes, ncclChar, r, c->nccl_comm,
+                                     c->stream));
+    EIGSOL_NCCL(nccl().GroupEnd());
+    EIGSOL_CUDA(cudaMemcpyAsync(out.data(), d.p, out.size(), cudaMemcpyDeviceToHost, c->stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
+    return out;
+}
+
+// min over ranks of an int (setup only): lets every rank take the same decision
+static int comm_min_int(Comm* c, int v) {
+    if (c->nranks == 1) return v;
+    int* d = reinterpret_cast<int*>(c->scratch.as<int64_t>() + 3 * c->nranks + 8);
+    EIGSOL_CUDA(cudaMemcpyAsync(d, &v, sizeof v, cudaMemcpyHostToDevice, c->stream));
+    EIGSOL_NCCL(nccl().AllReduce(d, d, 1, ncclInt32, ncclMin, c->nccl_comm, c->stream));
+    EIGSOL_CUDA(cudaMemcpyAsync(&v, d, sizeof v, cudaMemcpyDeviceToHost, c->stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
+    return v;
+}
+
 // -------------------------------------------------------------------------------------------------
 // The device-resident matrix + iteration state behind an eigsol_b200_matrix handle.
 // -------------------------------------------------------------------------------------------------
@@ -89,6 +116,11 @@ struct MatrixImpl {
     std::vector<char> send_contig;
     bool need_pack = false;
     DevBuf d_send_idx, d_sendbuf;
+    // x exchange + scalar all-reduce: MODE_FUSED (one GPU), MODE_SPLIT (NCCL), MODE_PEER (peer memory)
+    int xmode = MODE_FUSED;
+    PeerArgs peer_h{};
+    DevBuf d_peer, d_scal_in, d_flag_in;
+    std::vector<void*> ipc_opened;
 
     // sparse layouts
     CsrHost csr;  // local rows, localized columns (kept on the host to rebuild layouts)
@@ -123,6 +155,7 @@ struct MatrixImpl {
 
     int ss() const { return dtype ? 16 : 8; }
     ~MatrixImpl() {
+        for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
         if (graph) cudaGraphExecDestroy(graph);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
@@ -133,6 +166,11 @@ struct MatrixImpl {
     void init_sparse_local(CsrHost&& local_global_cols);
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
     void plan_exchange();
+    void setup_peer();
+    template <class S> IterArgs<S> iter_args() {
+        return IterArgs<S>{buf[0].as<S>(), buf[1].as<S>(), d_state.as<PowerState>(), d_partials.as<double>(), xmode,
+                           xmode == MODE_PEER ? d_peer.as<PeerArgs>() : nullptr};
+    }
     void alloc_vectors();
     void set_kernel(int kernel_, int lanes_);
     void configure_launch();
@@ -140,7 +178,7 @@ struct MatrixImpl {
 
     void begin(const void* x0, int max_it, double tol);
     void exchange_halo(int in);
-    void launch_matvec(int fused);
+    void launch_matvec();
     void issue_trips(int k);
     void step(int trips, float* ms_out);
     void end(void* x_out, double lambda_out[2], int* iters, int* conv);
@@ -249,6 +287,97 @@ void MatrixImpl::plan_exchange() {
 }
 
 // -------------------------------------------------------------------------------------------------
+// MODE_PEER wiring: every rank exports its two vector buffers, its scal_in and its flag_in through
+// CUDA IPC; peers map them and from then on the matvec kernel itself stores boundary rows, partial sums
+// and completion flags straight into peer memory over NVLink (kernels.cuh, PeerArgs).  Falls back to
+// MODE_SPLIT (NCCL send/recv + all-reduce) when IPC mapping is not possible on some rank.
+// -------------------------------------------------------------------------------------------------
+struct PeerBlob {
+    cudaIpcMemHandle_t buf[2], scal, flag;
+    int64_t halo_base;                 // nloc_pad: where the halo segment starts in the vector buffers
+    int64_t peer_off[kMaxPeers + 1];   // offset of each owner's entries inside the halo segment
+};
+
+void MatrixImpl::setup_peer() {
+    xmode = nranks == 1 ? MODE_FUSED : MODE_SPLIT;
+    if (nranks == 1) return;
+    const char* want = std::getenv("EIGSOL_B200_EXCHANGE");
+    const bool force_nccl = want && std::string(want) == "nccl";
+    d_scal_in.alloc(sizeof(double) * 2 * kMaxPeers * 4);
+    d_flag_in.alloc(sizeof(unsigned long long) * kMaxPeers);
+    PeerBlob mine;
+    std::memset(&mine, 0, sizeof mine);
+    int ok = (nranks <= kMaxPeers && !force_nccl) ? 1 : 0;
+    if (ok) {
+        ok &= cudaIpcGetMemHandle(&mine.buf[0], buf[0].p) == cudaSuccess;
+        ok &= cudaIpcGetMemHandle(&mine.buf[1], buf[1].p) == cudaSuccess;
+        ok &= cudaIpcGetMemHandle(&mine.scal, d_scal_in.p) == cudaSuccess;
+        ok &= cudaIpcGetMemHandle(&mine.flag, d_flag_in.p) == cudaSuccess;
+        cudaGetLastError();
+    }
+    mine.halo_base = nloc_pad;
+    for (int q = 0; q <= nranks && q <= kMaxPeers; ++q) mine.peer_off[q] = halo.peer_off[q];
+    ok = comm_min_int(comm, ok);
+    if (!ok) return;
+    const std::vector<char> all = comm_allgather_bytes(comm, &mine, sizeof mine);
+    PeerArgs pa;
+    std::memset(&pa, 0, sizeof pa);
+    pa.nranks = nranks;
+    pa.rank = rank;
+    pa.scal_in = d_scal_in.as<double>();
+    pa.flag_in = d_flag_in.as<unsigned long long>();
+    pa.send_idx = d_send_idx.as<int32_t>();
+    pa.spin_limit = (long long)env_int("EIGSOL_B200_PEER_TIMEOUT_MS", 4000) * 2000000LL;  // ~2 GHz ticks
+    const size_t es = size_t(ss());
+    int mapped = 1;
+    for (int q = 0; q < nranks && mapped; ++q) {
+        if (q == rank) continue;
+        PeerBlob pb;
+        std::memcpy(&pb, all.data() + sizeof(PeerBlob) * q, sizeof pb);
+        void* rb[2] = {nullptr, nullptr};
+        void *rs = nullptr, *rf = nullptr;
+        auto open = [&](void** dst, const cudaIpcMemHandle_t& h) {
+            if (cudaIpcOpenMemHandle(dst, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                mapped = 0;
+                return;
+            }
+            ipc_opened.push_back(*dst);
+        };
+        open(&rb[0], pb.buf[0]);
+        if (mapped) open(&rb[1], pb.buf[1]);
+        if (mapped) open(&rs, pb.scal);
+        if (mapped) open(&rf, pb.flag);
+        if (!mapped) break;
+        pa.peer_scal[q] = static_cast<double*>(rs);
+        pa.peer_flag[q] = static_cast<unsigned long long*>(rf) + rank;
+        if (send_count[q] == 0) continue;
+        const size_t dst_off = size_t(pb.halo_base + pb.peer_off[rank]) * es;
+        if (send_contig[q]) {
+            const int k = pa.nsend++;
+            pa.send_start[k] = int(send_start[q]);
+            pa.send_count[k] = int(send_count[q]);
+            for (int b = 0; b < 2; ++b) pa.send_dst[k][b] = static_cast<char*>(rb[b]) + dst_off;
+        } else {
+            const int k = pa.nlist++;
+            pa.list_off[k] = int(send_off[q]);
+            pa.list_count[k] = int(send_count[q]);
+            for (int b = 0; b < 2; ++b) pa.list_dst[k][b] = static_cast<char*>(rb[b]) + dst_off;
+        }
+    }
+    mapped = comm_min_int(comm, mapped);
+    if (!mapped) {
+        for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
+        ipc_opened.clear();
+        return;
+    }
+    peer_h = pa;
+    d_peer.alloc(sizeof(PeerArgs));
+    EIGSOL_CUDA(cudaMemcpy(d_peer.p, &pa, sizeof pa, cudaMemcpyHostToDevice));
+    xmode = MODE_PEER;
+}
+
+// -------------------------------------------------------------------------------------------------
 // Sparse: local rows in CSR with GLOBAL columns -> halo plan, localized columns, layouts, vectors.
 // row_begin must be set.
 // -------------------------------------------------------------------------------------------------
@@ -267,6 +396,7 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     localize_columns(local_nnz, csr.colidx.data(), lo, hi, nloc_pad, halo.cols);
     csr.cols = ext_len;
     plan_exchange();
+    setup_peer();
     stats = row_stats(nloc, csr.rowptr.data());
     if (nranks > 1) {
         const std::vector<int64_t> all = comm_allgather_i64(comm, local_nnz);
@@ -375,6 +505,7 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
     nhalo = int64_t(halo.cols.size());
     alloc_vectors();
     plan_exchange();
+    setup_peer();
     stats = RowStats();
     stats.rows = nloc;
     stats.nnz = local_nnz;
@@ -460,9 +591,9 @@ void MatrixImpl::configure_launch() {
 
 // One matvec launch on `stream`.  All launches of a handle are identical (the kernels pick the
 // ping-pong buffer from the device state), which is what lets a CUDA graph of them be replayed.
-template <class S> static void launch_sparse(MatrixImpl& m, int fused) {
+template <class S> static void launch_sparse(MatrixImpl& m) {
     constexpr int B = 256;
-    IterArgs<S> it{m.buf[0].as<S>(), m.buf[1].as<S>(), m.d_state.as<PowerState>(), m.d_partials.as<double>(), fused};
+    IterArgs<S> it = m.iter_args<S>();
     CsrView<S> A{int32_t(m.nloc), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
     const dim3 g(m.grid), b(B);
     cudaStream_t st = m.stream;
@@ -489,21 +620,21 @@ template <class S> static void launch_sparse(MatrixImpl& m, int fused) {
     }
 }
 
-template <class S> static void launch_dense(MatrixImpl& m, int fused) {
+template <class S> static void launch_dense(MatrixImpl& m) {
     constexpr int B = 256;
-    IterArgs<S> it{m.buf[0].as<S>(), m.buf[1].as<S>(), m.d_state.as<PowerState>(), m.d_partials.as<double>(), fused};
+    IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
     gemv_colmajor_kernel<S, B><<<dim3(m.grid), dim3(B), 0, m.stream>>>(A, it);
 }
 
-void MatrixImpl::launch_matvec(int fused) {
+void MatrixImpl::launch_matvec() {
     if (dense) {
-        if (dtype) launch_dense<double2>(*this, fused);
-        else launch_dense<double>(*this, fused);
+        if (dtype) launch_dense<double2>(*this);
+        else launch_dense<double>(*this);
     } else {
-        if (dtype) launch_sparse<double2>(*this, fused);
-        else launch_sparse<double>(*this, fused);
+        if (dtype) launch_sparse<double2>(*this);
+        else launch_sparse<double>(*this);
     }
     ++launches;
 }
@@ -531,6 +662,23 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol) {
         EIGSOL_CUDA(cudaMemcpyAsync(buf[0].p, static_cast<const char*>(x0) + size_t(lo) * s, size_t(nloc) * s,
                                     cudaMemcpyHostToDevice, stream));
     if (dense) EIGSOL_CUDA(cudaMemsetAsync(d_tile_ticket.p, 0, sizeof(unsigned) * size_t(ntiles), stream));
+    if (nranks > 1) {
+        // x0 is global on every rank: the halo of launch 0 comes straight from it (no exchange needed)
+        if (nhalo) {
+            std::vector<char> hx(size_t(nhalo) * s);
+            const char* src = static_cast<const char*>(x0);
+            for (int64_t k = 0; k < nhalo; ++k) std::memcpy(hx.data() + size_t(k) * s, src + size_t(halo.cols[k]) * s, s);
+            EIGSOL_CUDA(cudaMemcpyAsync(buf[0].as<char>() + size_t(nloc_pad) * s, hx.data(), hx.size(),
+                                        cudaMemcpyHostToDevice, stream));
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        }
+        if (xmode == MODE_PEER) {
+            EIGSOL_CUDA(cudaMemsetAsync(d_scal_in.p, 0, d_scal_in.bytes, stream));
+            EIGSOL_CUDA(cudaMemsetAsync(d_flag_in.p, 0, d_flag_in.bytes, stream));
+        }
+        // barrier: no rank may start launching (and storing into peers) before every rank has reset
+        EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 1, ncclDouble, ncclSum, comm->nccl_comm, stream));
+    }
     EIGSOL_CUDA(cudaStreamSynchronize(stream));  // x0 is a borrowed host pointer
     begun = true;
 }
@@ -574,7 +722,7 @@ void MatrixImpl::exchange_halo(int in) {
 void MatrixImpl::issue_trips(int k) {
     if (k <= 0) return;
     EIGSOL_CUDA(cudaSetDevice(device));
-    if (nranks == 1) {
+    if (xmode != MODE_SPLIT) {
         const int glen = env_int("EIGSOL_B200_GRAPH", 16);
         if (glen > 1 && k >= glen) {
             if (!graph || graph_len != glen) {
@@ -582,7 +730,7 @@ void MatrixImpl::issue_trips(int k) {
                 cudaGraph_t g = nullptr;
                 EIGSOL_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
                 const int64_t keep = launches;
-                for (int i = 0; i < glen; ++i) launch_matvec(1);
+                for (int i = 0; i < glen; ++i) launch_matvec();
                 launches = keep;
                 EIGSOL_CUDA(cudaStreamEndCapture(stream, &g));
                 EIGSOL_CUDA(cudaGraphInstantiate(&graph, g, 0));
@@ -597,7 +745,7 @@ void MatrixImpl::issue_trips(int k) {
             }
         }
         for (int i = 0; i < k; ++i) {
-            launch_matvec(1);
+            launch_matvec();
             ++issued;
         }
         EIGSOL_CUDA(cudaGetLastError());
@@ -605,7 +753,7 @@ void MatrixImpl::issue_trips(int k) {
     }
     for (int i = 0; i < k; ++i) {
         exchange_halo(issued & 1);
-        launch_matvec(0);
+        launch_matvec();
         reduce_partials_kernel<256><<<1, 256, 0, stream>>>(d_partials.as<double>(), nslots, d_state.as<PowerState>(),
                                                           d_scal.as<double>());
         EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 3, ncclDouble, ncclSum, comm->nccl_comm, stream));
@@ -617,8 +765,17 @@ void MatrixImpl::issue_trips(int k) {
 }
 
 const PowerState& MatrixImpl::poll_state() {
+    if (xmode == MODE_PEER) {
+        // fold the sums of the last executed launch into the state (waits for the peers' flags)
+        if (dtype) peer_flush_kernel<double2><<<1, 32, 0, stream>>>(iter_args<double2>());
+        else peer_flush_kernel<double><<<1, 32, 0, stream>>>(iter_args<double>());
+        ++launches;
+    }
     EIGSOL_CUDA(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(PowerState), cudaMemcpyDeviceToHost, stream));
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    if (h_state.as<PowerState>()->stop == STOP_ERROR)
+        throw DeviceError("powerMethod: device error: a peer GPU did not signal within the timeout "
+                          "(EIGSOL_B200_PEER_TIMEOUT_MS); the ranks are out of step");
     return *h_state.as<PowerState>();
 }
 
@@ -729,11 +886,12 @@ void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
     info->nranks = nranks;
     info->rank = rank;
     int per_trip = 1;
-    if (nranks > 1) {
+    if (xmode == MODE_SPLIT) {
         per_trip += 2;
         for (int q = 0; q < nranks; ++q)
             if (send_count[q] > 0 && !send_contig[q]) ++per_trip;
     }
+    info->exchange = xmode;
     info->kernels_per_trip = per_trip;
 }
 

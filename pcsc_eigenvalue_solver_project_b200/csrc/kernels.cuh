@@ -36,9 +36,12 @@ struct PowerState {
     int converged;
     int final_buf;      // buffer whose normalisation is EigenResult::eigenvector
     unsigned ticket;    // CTA completion counter of the running launch
+    int pending;        // MODE_PEER: launch `launches` has run but its global sums are not folded in yet
+    int reserved;
 };
 
-enum { STOP_NONE = 0, STOP_CONVERGED = 1, STOP_ZERO_NORM = 2, STOP_MAX_TRIPS = 3 };
+enum { STOP_NONE = 0, STOP_CONVERGED = 1, STOP_ZERO_NORM = 2, STOP_MAX_TRIPS = 3,
+       STOP_ERROR = 4 };  // a peer never signalled (MODE_PEER wait timed out)
 
 // -------------------------------------------------------------------------------------------------
 // Scalar traits: double and complex<double> (as double2 = interleaved re, im).
@@ -155,13 +158,44 @@ template <class S> struct DenseView {
     unsigned* tile_ticket;  // [ntiles]
 };
 
+// How the grid-level finish of a launch is done.
+enum { MODE_FUSED = 0,   // one GPU: the last CTA sums the partials and runs the convergence test
+       MODE_SPLIT = 1,   // N GPUs over NCCL: partials only; reduce + all-reduce + finalize_kernel follow
+       MODE_PEER = 2 };  // N GPUs over peer memory: ONE kernel per iteration does matvec + x exchange +
+                         // scalar all-reduce (P2P stores over NVLink, flags with system-scope release/acquire)
+
+constexpr int kMaxPeers = 8;
+
+// Multi-GPU peer-memory wiring of one rank (MODE_PEER).  Every rank runs the same launch sequence in
+// lock step: launch l reads buffer l&1 (own rows + halo) and writes buffer (l+1)&1.  Rows of z that a
+// peer's rows reference are ALSO stored straight into that peer's halo region of ITS buffer (l+1)&1,
+// the rank's three partial sums go to every peer's scal_in[l&1][rank], and finally flag_in[rank] on every
+// peer is set to l+1 (release).  Launch l+1 starts by waiting for all its flag_in[q] >= l+1 (acquire).
+struct PeerArgs {
+    int nranks, rank;
+    int nsend;                        // contiguous send ranges (rows stored remotely as they are produced)
+    int send_start[kMaxPeers];        // first local row of the range
+    int send_count[kMaxPeers];
+    void* send_dst[kMaxPeers][2];     // remote address of the peer's halo segment, per buffer parity
+    int nlist;                        // scattered send lists (copied by the last CTA)
+    int list_off[kMaxPeers], list_count[kMaxPeers];
+    void* list_dst[kMaxPeers][2];
+    const int32_t* send_idx;          // local row indices of the scattered lists
+    double* peer_scal[kMaxPeers];     // remote scal_in base of rank q (nullptr for self)
+    unsigned long long* peer_flag[kMaxPeers];  // remote &flag_in[rank] of rank q
+    double* scal_in;                  // local [2][kMaxPeers][4]
+    unsigned long long* flag_in;      // local [kMaxPeers]
+    long long spin_limit;             // clock64 ticks before a wait gives up (STOP_ERROR)
+};
+
 // Everything a matvec launch needs besides the matrix.
 template <class S> struct IterArgs {
     S* buf0;             // ping-pong vector buffers, extended layout [local | halo]
     S* buf1;
     PowerState* st;
     double* partials;    // 3 doubles per CTA slot: d_re, d_im, q'
-    int fused_finalize;  // 1: last CTA reduces partials and runs the convergence test (single GPU)
+    int mode;            // MODE_*
+    const PeerArgs* peer;  // device copy (MODE_PEER), else nullptr
 };
 
 // -------------------------------------------------------------------------------------------------
@@ -199,36 +233,43 @@ __device__ __forceinline__ void finalize_launch(PowerState* st, double dre, doub
     st->ticket = 0;
 }
 
-// Per-launch prologue, executed by every thread: returns false when the launch must be a no-op
-// (already stopped, past maxIterations, or ||y|| == 0 -- power_method.hpp:73-76).
+// trip k = l-1 found normY == 0 (power_method.hpp:73-76): x and lambda stay those of the previous
+// trip, usedIters = k+1.
+__device__ __forceinline__ void zero_norm_stop(PowerState* st, int l, int in) {
+    st->trips = l;
+    st->final_buf = in ^ 1;
+    st->final_q = st->q[in ^ 1];
+    st->stop = STOP_ZERO_NORM;
+}
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_volatile_f64(const double* p) {
+    double v;
+    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Per-launch context (kept small: it lives in registers across the matvec loop).  The state AFTER
+// everything a launch learns in its prologue (the deferred finalize of the previous launch in MODE_PEER,
+// a zero-norm stop) is a pure function of the state in memory and the peers' sums, so every thread of
+// every CTA derives the same decision, and the last CTA to finish re-derives the full state and is the
+// only one that writes it back: no CTA ever reads a half-updated state.
 struct LaunchCtx {
     int l, in;
     double qin, s;
+    int dirty;    // the derived state differs from the state in memory
+    int wait_ok;  // MODE_PEER: every peer signalled in time
 };
 
-__device__ __forceinline__ bool launch_prologue(PowerState* st, LaunchCtx& c) {
-    const int stop = st->stop;
-    c.l = st->launches;
-    if (stop != STOP_NONE || c.l > st->max_trips) return false;
-    c.in = c.l & 1;
-    c.qin = st->q[c.in];
-    if (c.qin == 0.0) {
-        // trip k = l-1 found normY == 0: x and lambda stay those of the previous trip, usedIters = k+1.
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            st->trips = c.l;
-            st->final_buf = c.in ^ 1;
-            st->final_q = st->q[c.in ^ 1];
-            st->stop = STOP_ZERO_NORM;
-        }
-        return false;
-    }
-    c.s = 1.0 / sqrt(c.qin);
-    return true;
-}
-
 // -------------------------------------------------------------------------------------------------
-// CTA reduction of the three running sums + (optionally) the grid-level finish.
-// Deterministic: fixed shuffle tree inside the CTA, fixed-order sum over CTA slots in the last CTA.
+// CTA reduction of the three running sums.  Deterministic: fixed shuffle tree inside the CTA.
 // -------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -259,22 +300,114 @@ __device__ __forceinline__ void cta_sum3(double& a, double& b, double& c, double
     __syncthreads();
 }
 
-// slot / nslots: which partial slot this CTA owns and how many CTAs will report.
-template <int BLOCK>
-__device__ __forceinline__ void grid_finish(PowerState* st, double* partials, int fused, const LaunchCtx& c,
-                                            double dre, double dim, double qn, int slot, int nslots) {
+// -------------------------------------------------------------------------------------------------
+// Per-launch prologue, executed by every thread: returns false when the launch must be a no-op
+// (already stopped, past maxIterations, ||y|| == 0, or a peer wait timed out).
+// MODE_PEER: first wait until every peer has finished the previous launch (its halo rows and partial
+// sums have landed here), add the partial sums in rank order and run the deferred finalize.
+// -------------------------------------------------------------------------------------------------
+// Derives (ns, c) from the state in memory; returns true when the launch is active.  No barriers.
+template <class S>
+__device__ __noinline__ bool derive_state(const IterArgs<S>& it, PowerState& ns, LaunchCtx& c) {
+    ns = *it.st;
+    c.dirty = 0;
+    if (ns.stop != STOP_NONE) return false;
+    if (it.mode == MODE_PEER && ns.pending) {
+        const PeerArgs& pa = *it.peer;
+        const int lp = ns.launches;  // executed, not yet finalized
+        c.dirty = 1;
+        if (!c.wait_ok) {
+            ns.stop = STOP_ERROR;
+            return false;
+        }
+        double a = 0.0, b = 0.0, d = 0.0;
+        const double* sc = pa.scal_in + (lp & 1) * kMaxPeers * 4;
+        for (int q = 0; q < pa.nranks; ++q) {
+            a += ld_volatile_f64(sc + 4 * q + 0);
+            b += ld_volatile_f64(sc + 4 * q + 1);
+            d += ld_volatile_f64(sc + 4 * q + 2);
+        }
+        finalize_launch(&ns, a, b, d, lp, lp & 1, ns.q[lp & 1]);
+        ns.pending = 0;
+        if (ns.stop != STOP_NONE) return false;
+    }
+    c.l = ns.launches;
+    if (c.l > ns.max_trips) return false;
+    c.in = c.l & 1;
+    c.qin = ns.q[c.in];
+    if (c.qin == 0.0) {
+        if (it.mode != MODE_SPLIT) {  // MODE_SPLIT: finalize_kernel takes the decision
+            zero_norm_stop(&ns, c.l, c.in);
+            c.dirty = 1;
+        }
+        return false;
+    }
+    c.s = 1.0 / sqrt(c.qin);
+    return true;
+}
+
+template <class S, int BLOCK>
+__device__ __forceinline__ bool launch_prologue(const IterArgs<S>& it, LaunchCtx& c) {
+    __shared__ int s_wait_ok;
+    c.wait_ok = 1;
+    if (it.mode == MODE_PEER) {
+        if (threadIdx.x == 0) {
+            int ok = 1;
+            if (it.st->stop == STOP_NONE && it.st->pending) {
+                const PeerArgs& pa = *it.peer;
+                const unsigned long long want = (unsigned long long)(it.st->launches + 1);
+                const long long t0 = clock64();
+                for (int q = 0; q < pa.nranks && ok; ++q) {
+                    if (q == pa.rank) continue;
+                    while (ld_acquire_sys(pa.flag_in + q) < want) {
+                        if (clock64() - t0 > pa.spin_limit) {
+                            ok = 0;
+                            break;
+                        }
+                    }
+                }
+            }
+            s_wait_ok = ok;
+        }
+        __syncthreads();
+        c.wait_ok = s_wait_ok;
+    }
+    PowerState ns;
+    return derive_state<S>(it, ns, c);
+}
+
+// No-op launch: if the prologue changed the state, the last CTA to get here writes it back.
+template <class S>
+__device__ __forceinline__ void finish_inactive(const IterArgs<S>& it, LaunchCtx& c) {
+    if (!c.dirty || threadIdx.x != 0) return;
+    const unsigned t = atomicAdd(&it.st->ticket, 1u);
+    if (t == gridDim.x - 1) {
+        PowerState ns;
+        derive_state<S>(it, ns, c);
+        ns.ticket = 0;
+        *it.st = ns;
+    }
+}
+
+// Active launch: CTA sums -> partial slot; the last CTA adds the slots in fixed order and either runs
+// the convergence test (MODE_FUSED) or publishes this rank's sums and its completion flag to every peer
+// (MODE_PEER).  slot / nslots: which partial slot this CTA owns and how many CTAs will report.
+template <class S, int BLOCK>
+__device__ __forceinline__ void grid_finish(const IterArgs<S>& it, LaunchCtx& c, double dre, double dim, double qn,
+                                            int slot, int nslots) {
     __shared__ double sred[3][BLOCK / 32];
     __shared__ int s_last;
     cta_sum3<BLOCK>(dre, dim, qn, sred);
     if (threadIdx.x == 0) {
-        partials[3 * slot + 0] = dre;
-        partials[3 * slot + 1] = dim;
-        partials[3 * slot + 2] = qn;
+        it.partials[3 * slot + 0] = dre;
+        it.partials[3 * slot + 1] = dim;
+        it.partials[3 * slot + 2] = qn;
     }
-    if (!fused) return;
+    if (it.mode == MODE_SPLIT) return;
     if (threadIdx.x == 0) {
-        __threadfence();
-        const unsigned t = atomicAdd(&st->ticket, 1u);
+        if (it.mode == MODE_PEER) __threadfence_system();  // this CTA's remote halo stores
+        else __threadfence();
+        const unsigned t = atomicAdd(&it.st->ticket, 1u);
         s_last = (t == unsigned(nslots - 1));
     }
     __syncthreads();
@@ -282,22 +415,72 @@ __device__ __forceinline__ void grid_finish(PowerState* st, double* partials, in
     __threadfence();
     double a = 0.0, b = 0.0, d = 0.0;
     for (int i = threadIdx.x; i < nslots; i += BLOCK) {
-        a += __ldcg(partials + 3 * i + 0);
-        b += __ldcg(partials + 3 * i + 1);
-        d += __ldcg(partials + 3 * i + 2);
+        a += __ldcg(it.partials + 3 * i + 0);
+        b += __ldcg(it.partials + 3 * i + 1);
+        d += __ldcg(it.partials + 3 * i + 2);
     }
     cta_sum3<BLOCK>(a, b, d, sred);
-    if (threadIdx.x == 0) finalize_launch(st, a, b, d, c.l, c.in, c.qin);
+    if (it.mode == MODE_FUSED) {
+        if (threadIdx.x == 0) {
+            PowerState ns;
+            derive_state<S>(it, ns, c);
+            finalize_launch(&ns, a, b, d, c.l, c.in, c.qin);
+            ns.ticket = 0;
+            *it.st = ns;
+        }
+        return;
+    }
+    // MODE_PEER
+    const PeerArgs& pa = *it.peer;
+    const int par = c.l & 1;
+    // scattered send lists: rows other CTAs wrote, copied to the peers' halo segments
+    const S* outv = par ? it.buf0 : it.buf1;
+    for (int k = 0; k < pa.nlist; ++k) {
+        S* dst = static_cast<S*>(pa.list_dst[k][par ^ 1]);
+        const int32_t* idx = pa.send_idx + pa.list_off[k];
+        for (int i = threadIdx.x; i < pa.list_count[k]; i += BLOCK) dst[i] = Sc<S>::ldcg(outv + idx[i]);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double* mine = pa.scal_in + par * kMaxPeers * 4 + pa.rank * 4;
+        mine[0] = a;
+        mine[1] = b;
+        mine[2] = d;
+        for (int q = 0; q < pa.nranks; ++q) {
+            if (q == pa.rank) continue;
+            double* dst = pa.peer_scal[q] + par * kMaxPeers * 4 + pa.rank * 4;
+            dst[0] = a;
+            dst[1] = b;
+            dst[2] = d;
+        }
+        PowerState ns;
+        derive_state<S>(it, ns, c);
+        ns.pending = 1;
+        ns.ticket = 0;
+        *it.st = ns;
+        __threadfence_system();
+        for (int q = 0; q < pa.nranks; ++q)
+            if (q != pa.rank) st_release_sys(pa.peer_flag[q], (unsigned long long)(c.l + 1));
+    }
 }
 
-// Row epilogue shared by every matvec kernel: z is (A u)_row * s already.
+// Row epilogue shared by every matvec kernel: z is (A u)_row * s already.  In MODE_PEER a row that a
+// peer's rows reference is also stored into that peer's halo segment (fire-and-forget NVLink store).
 template <class S>
-__device__ __forceinline__ void row_epilogue(S z, S u_own, double s, S* out, int row, double& dre, double& dim,
-                                             double& qn) {
-    const S x = Sc<S>::scale(u_own, s);
+__device__ __forceinline__ void row_epilogue(const IterArgs<S>& it, const LaunchCtx& c, S z, S u_own, S* out, int row,
+                                             double& dre, double& dim, double& qn) {
+    const S x = Sc<S>::scale(u_own, c.s);
     Sc<S>::dotc(x, z, dre, dim);
     qn += Sc<S>::abs2(z);
     out[row] = z;
+    if (it.mode == MODE_PEER) {
+        const PeerArgs& pa = *it.peer;
+        for (int k = 0; k < pa.nsend; ++k) {
+            const unsigned off = unsigned(row - pa.send_start[k]);
+            if (off < unsigned(pa.send_count[k])) static_cast<S*>(pa.send_dst[k][(c.in ^ 1)])[off] = z;
+        }
+    }
 }
 
 // =================================================================================================
@@ -307,7 +490,10 @@ __device__ __forceinline__ void row_epilogue(S z, S u_own, double s, S* out, int
 template <class S, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it) {
     LaunchCtx c;
-    if (!launch_prologue(it.st, c)) return;
+    if (!launch_prologue<S, BLOCK>(it, c)) {
+        finish_inactive<S>(it, c);
+        return;
+    }
     const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
     S* __restrict__ out = c.in ? it.buf0 : it.buf1;
     double dre = 0.0, dim = 0.0, qn = 0.0;
@@ -315,9 +501,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
         const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
         S acc = Sc<S>::zero();
         for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), Sc<S>::ldg(u + __ldg(A.colidx + p)));
-        row_epilogue<S>(Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), c.s, out, row, dre, dim, qn);
+        row_epilogue<S>(it, c, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, dre, dim, qn);
     }
-    grid_finish<BLOCK>(it.st, it.partials, it.fused_finalize, c, dre, dim, qn, blockIdx.x, gridDim.x);
+    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
 }
 
 // =================================================================================================
@@ -327,7 +513,10 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
 template <class S, int LANES, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, IterArgs<S> it) {
     LaunchCtx c;
-    if (!launch_prologue(it.st, c)) return;
+    if (!launch_prologue<S, BLOCK>(it, c)) {
+        finish_inactive<S>(it, c);
+        return;
+    }
     const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
     S* __restrict__ out = c.in ? it.buf0 : it.buf1;
     double dre = 0.0, dim = 0.0, qn = 0.0;
@@ -346,9 +535,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
 #pragma unroll
         for (int d = LANES / 2; d > 0; d >>= 1) Sc<S>::add(acc, Sc<S>::shfl_down(acc, d, LANES));
         if (sub == 0 && row < A.rows)
-            row_epilogue<S>(Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), c.s, out, row, dre, dim, qn);
+            row_epilogue<S>(it, c, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, dre, dim, qn);
     }
-    grid_finish<BLOCK>(it.st, it.partials, it.fused_finalize, c, dre, dim, qn, blockIdx.x, gridDim.x);
+    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
 }
 
 // =================================================================================================
@@ -371,7 +560,10 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
     __shared__ int32_t srow[kStreamMaxRows + 1];
     __shared__ double slong[3][BLOCK / 32];
     LaunchCtx c;
-    if (!launch_prologue(it.st, c)) return;
+    if (!launch_prologue<S, BLOCK>(it, c)) {
+        finish_inactive<S>(it, c);
+        return;
+    }
     const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
     S* __restrict__ out = c.in ? it.buf0 : it.buf1;
     double dre = 0.0, dim = 0.0, qn = 0.0;
@@ -400,7 +592,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                 S z;
                 if constexpr (Sc<S>::is_complex) z = make_double2(ar * c.s, ai * c.s);
                 else z = ar * c.s;
-                row_epilogue<S>(z, Sc<S>::ldg(u + r0), c.s, out, r0, dre, dim, qn);
+                row_epilogue<S>(it, c, z, Sc<S>::ldg(u + r0), out, r0, dre, dim, qn);
             }
         } else {
             for (int e = base + 2 * threadIdx.x; e < p1; e += 2 * BLOCK) {
@@ -422,12 +614,12 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                 S acc = Sc<S>::zero();
                 const int q1 = srow[i + 1] - base;
                 for (int q = srow[i] - base; q < q1; ++q) Sc<S>::add(acc, prod[q]);
-                row_epilogue<S>(Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + r0 + i), c.s, out, r0 + i, dre, dim, qn);
+                row_epilogue<S>(it, c, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + r0 + i), out, r0 + i, dre, dim, qn);
             }
         }
         __syncthreads();
     }
-    grid_finish<BLOCK>(it.st, it.partials, it.fused_finalize, c, dre, dim, qn, blockIdx.x, gridDim.x);
+    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
 }
 
 // =================================================================================================
@@ -440,7 +632,10 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
 template <class S, int R, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArgs<S> it) {
     LaunchCtx c;
-    if (!launch_prologue(it.st, c)) return;
+    if (!launch_prologue<S, BLOCK>(it, c)) {
+        finish_inactive<S>(it, c);
+        return;
+    }
     const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
     S* __restrict__ out = c.in ? it.buf0 : it.buf1;
     double dre = 0.0, dim = 0.0, qn = 0.0;
@@ -485,9 +680,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 #pragma unroll
         for (int r = 0; r < R; ++r)
             if (row + r < A.rows)
-                row_epilogue<S>(Sc<S>::scale(acc[r], c.s), Sc<S>::ldg(u + row + r), c.s, out, row + r, dre, dim, qn);
+                row_epilogue<S>(it, c, Sc<S>::scale(acc[r], c.s), Sc<S>::ldg(u + row + r), out, row + r, dre, dim, qn);
     }
-    grid_finish<BLOCK>(it.st, it.partials, it.fused_finalize, c, dre, dim, qn, blockIdx.x, gridDim.x);
+    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
 }
 
 // =================================================================================================
@@ -505,7 +700,10 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     __shared__ __align__(16) S xs[kGemvChunk];
     __shared__ int s_tile_last;
     LaunchCtx c;
-    if (!launch_prologue(it.st, c)) return;
+    if (!launch_prologue<S, BLOCK>(it, c)) {
+        finish_inactive<S>(it, c);
+        return;
+    }
     const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
     S* __restrict__ out = c.in ? it.buf0 : it.buf1;
     const int tile = blockIdx.x / A.nseg, seg = blockIdx.x % A.nseg;
@@ -556,10 +754,10 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
         if (row < A.rows) {
             S z = Sc<S>::zero();
             for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
-            row_epilogue<S>(z, Sc<S>::ldg(u + row), c.s, out, row, dre, dim, qn);
+            row_epilogue<S>(it, c, z, Sc<S>::ldg(u + row), out, row, dre, dim, qn);
         }
     }
-    grid_finish<BLOCK>(it.st, it.partials, it.fused_finalize, c, dre, dim, qn, tile, A.ntiles);
+    grid_finish<S, BLOCK>(it, c, dre, dim, qn, tile, A.ntiles);
 }
 
 // =================================================================================================
@@ -596,13 +794,24 @@ __global__ void finalize_kernel(PowerState* st, const double* scal) {
     const int in = l & 1;
     const double qin = st->q[in];
     if (qin == 0.0) {
-        st->trips = l;
-        st->final_buf = in ^ 1;
-        st->final_q = st->q[in ^ 1];
-        st->stop = STOP_ZERO_NORM;
+        zero_norm_stop(st, l, in);
         return;
     }
     finalize_launch(st, scal[0], scal[1], scal[2], l, in, qin);
+}
+
+// MODE_PEER: folds the sums of the last executed launch into the state (run before the host reads it,
+// so that it sees the same state a single-GPU run would have after that launch).
+template <class S>
+__global__ void peer_flush_kernel(IterArgs<S> it) {
+    LaunchCtx c;
+    launch_prologue<S, 32>(it, c);
+    if (c.dirty && threadIdx.x == 0) {
+        PowerState ns;
+        derive_state<S>(it, ns, c);
+        ns.ticket = 0;
+        *it.st = ns;
+    }
 }
 
 // x = y / normY (power_method.hpp:78, true division) of the result buffer -> contiguous output.
