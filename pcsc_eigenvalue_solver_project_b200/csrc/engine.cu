@@ -328,6 +328,7 @@ void MatrixImpl::setup_peer() {
     pa.flag_in = d_flag_in.as<unsigned long long>();
     pa.send_idx = d_send_idx.as<int32_t>();
     pa.spin_limit = (long long)env_int("EIGSOL_B200_PEER_TIMEOUT_MS", 4000) * 2000000LL;  // ~2 GHz ticks
+    pa.debug = env_int("EIGSOL_B200_PEER_DEBUG", 0);
     const size_t es = size_t(ss());
     int mapped = 1;
     for (int q = 0; q < nranks && mapped; ++q) {

@@ -186,6 +186,7 @@ struct PeerArgs {
     double* scal_in;                  // local [2][kMaxPeers][4]
     unsigned long long* flag_in;      // local [kMaxPeers]
     long long spin_limit;             // clock64 ticks before a wait gives up (STOP_ERROR)
+    int debug;                        // TIMING EXPERIMENTS ONLY (EIGSOL_B200_PEER_DEBUG): 1 no sys fence per CTA, 2 no halo stores, 4 no wait, 8 no publish
 };
 
 // Everything a matvec launch needs besides the matrix.
@@ -353,7 +354,7 @@ __device__ __forceinline__ bool launch_prologue(const IterArgs<S>& it, LaunchCtx
     if (it.mode == MODE_PEER) {
         if (threadIdx.x == 0) {
             int ok = 1;
-            if (it.st->stop == STOP_NONE && it.st->pending) {
+            if (it.st->stop == STOP_NONE && it.st->pending && !(it.peer->debug & 4)) {
                 const PeerArgs& pa = *it.peer;
                 const unsigned long long want = (unsigned long long)(it.st->launches + 1);
                 const long long t0 = clock64();
@@ -405,7 +406,7 @@ __device__ __forceinline__ void grid_finish(const IterArgs<S>& it, LaunchCtx& c,
     }
     if (it.mode == MODE_SPLIT) return;
     if (threadIdx.x == 0) {
-        if (it.mode == MODE_PEER) __threadfence_system();  // this CTA's remote halo stores
+        if (it.mode == MODE_PEER && !(it.peer->debug & 1)) __threadfence_system();  // this CTA's remote halo stores
         else __threadfence();
         const unsigned t = atomicAdd(&it.st->ticket, 1u);
         s_last = (t == unsigned(nslots - 1));
@@ -447,7 +448,7 @@ __device__ __forceinline__ void grid_finish(const IterArgs<S>& it, LaunchCtx& c,
         mine[0] = a;
         mine[1] = b;
         mine[2] = d;
-        for (int q = 0; q < pa.nranks; ++q) {
+        for (int q = 0; q < pa.nranks && !(pa.debug & 8); ++q) {
             if (q == pa.rank) continue;
             double* dst = pa.peer_scal[q] + par * kMaxPeers * 4 + pa.rank * 4;
             dst[0] = a;
@@ -460,7 +461,7 @@ __device__ __forceinline__ void grid_finish(const IterArgs<S>& it, LaunchCtx& c,
         ns.ticket = 0;
         *it.st = ns;
         __threadfence_system();
-        for (int q = 0; q < pa.nranks; ++q)
+        for (int q = 0; q < pa.nranks && !(pa.debug & 8); ++q)
             if (q != pa.rank) st_release_sys(pa.peer_flag[q], (unsigned long long)(c.l + 1));
     }
 }
@@ -476,7 +477,7 @@ __device__ __forceinline__ void row_epilogue(const IterArgs<S>& it, const Launch
     out[row] = z;
     if (it.mode == MODE_PEER) {
         const PeerArgs& pa = *it.peer;
-        for (int k = 0; k < pa.nsend; ++k) {
+        for (int k = 0; k < pa.nsend && !(pa.debug & 2); ++k) {
             const unsigned off = unsigned(row - pa.send_start[k]);
             if (off < unsigned(pa.send_count[k])) static_cast<S*>(pa.send_dst[k][(c.in ^ 1)])[off] = z;
         }

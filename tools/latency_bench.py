@@ -1,0 +1,58 @@
+"""Per-trip latency floor of the power-iteration launch at small sizes (development tool).
+Run alone (N=1) or under torch.distributed.run (N>1).  Prints one JSON line per grid size:
+    python tools/latency_bench.py [g ...]        # 3D Laplacian g^3
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import pcsc_eigenvalue_solver_project_b200 as es
+from pcsc_eigenvalue_solver_project_b200 import generators as gen
+
+
+def main():
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    comm = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local))
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(es.Comm.unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        comm = es.Comm(rank, world, idt.cpu().numpy().tobytes(), local)
+    grids = [int(a) for a in sys.argv[1:]] or [16, 64, 128, 256]
+    for g in grids:
+        n = g ** 3
+        lo, hi = n * rank // world, n * (rank + 1) // world
+        rp, ci, v = gen.laplacian_3d(g, lo, hi)
+        dm = es.DeviceMatrix.from_csr_rows(n, lo, rp, ci, v, comm)
+        x0 = es.random_unit(n, np.float64, seed=1)
+        dm.begin(x0, 2 ** 31 - 2, -1.0)
+        dm.step(64)
+        best = 1e30
+        for _ in range(3):
+            ms = dm.step(320)
+            if comm is not None:
+                ms = comm.max_float(ms)
+            best = min(best, ms)
+        info = dm.info()
+        r = dm.end(want_vector=False)
+        if rank == 0:
+            print(json.dumps({"g": g, "n": n, "world": world, "us_per_trip": best / 320 * 1e3, "exchange": info["exchange"],
+                              "kernel": info["kernel_name"], "debug": os.environ.get("EIGSOL_B200_PEER_DEBUG", "0"),
+                              "alg_GBps_per_rank": info["alg_bytes"] / (best / 320 * 1e-3) / 1e9,
+                              "lambda": repr(r.eigenvalue)}), flush=True)
+        dm.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
