@@ -130,7 +130,11 @@ struct MatrixImpl {
     int sell_R = 0;
     int64_t sell_nslices = 0, sell_padded = 0;
     DevBuf d_rowblk;
+    std::vector<int32_t> rowblk_h;
     int nblk = 0;
+    DevBuf d_deferred;  // MODE_PEER: per work unit of the chosen kernel, 1 = reads halo entries
+    bool have_deferred = false;
+    int serpentine = 0;
 
     // dense layout
     DevBuf d_dense, d_dense_partial, d_tile_ticket;
@@ -138,7 +142,7 @@ struct MatrixImpl {
     int nseg = 1, ntiles = 1;
 
     // vectors and state
-    DevBuf buf[2], d_state, d_partials, d_scal, d_xloc, d_xglob;
+    DevBuf buf[kRing], d_state, d_partials, d_scal, d_xloc, d_xglob;
     PinnedBuf h_state;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -147,7 +151,8 @@ struct MatrixImpl {
     int kernel = K_CSR_SCALAR, lanes = 0, grid = 1, block = 256, nslots = 1;
     int64_t stored_bytes = 0;
     int64_t launches = 0;  // kernel launches issued over the handle's life
-    int issued = 0;        // matvec launches issued since begin (buffer parity on the host)
+    int issued = 0;        // matvec launches issued since begin (ring phase on the host)
+    unsigned long long flag_epoch = 0;  // MODE_PEER: flag base of the current solve (identical on every rank)
     bool begun = false;
     int max_trips = 0;
     cudaGraphExec_t graph = nullptr;
@@ -168,8 +173,17 @@ struct MatrixImpl {
     void plan_exchange();
     void setup_peer();
     template <class S> IterArgs<S> iter_args() {
-        return IterArgs<S>{buf[0].as<S>(), buf[1].as<S>(), d_state.as<PowerState>(), d_partials.as<double>(), xmode,
-                           xmode == MODE_PEER ? d_peer.as<PeerArgs>() : nullptr};
+        IterArgs<S> a;
+        for (int b = 0; b < kRing; ++b) a.buf[b] = buf[b].as<S>();
+        a.st = d_state.as<PowerState>();
+        a.partials = d_partials.as<double>();
+        a.nslots = nslots;
+        a.mode = xmode;
+        a.peer = xmode == MODE_PEER ? d_peer.as<PeerArgs>() : nullptr;
+        a.scal_glob = d_scal.as<double>();
+        a.deferred = (xmode == MODE_PEER && have_deferred) ? d_deferred.as<uint8_t>() : nullptr;
+        a.serpentine = serpentine;
+        return a;
     }
     void alloc_vectors();
     void set_kernel(int kernel_, int lanes_);
@@ -178,7 +192,8 @@ struct MatrixImpl {
 
     void begin(const void* x0, int max_it, double tol);
     void exchange_halo(int in);
-    void launch_matvec();
+    void launch_matvec(int phase);
+    void build_deferred();
     void issue_trips(int k);
     void step(int trips, float* ms_out);
     void end(void* x_out, double lambda_out[2], int* iters, int* conv);
@@ -208,7 +223,8 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     EIGSOL_CUDA(cudaEventCreate(&ev0));
     EIGSOL_CUDA(cudaEventCreate(&ev1));
     d_state.alloc(sizeof(PowerState));
-    d_scal.alloc(4 * sizeof(double));
+    d_scal.alloc(kRing * 4 * sizeof(double));
+    serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     h_state.alloc(sizeof(PowerState));
 }
 
@@ -293,7 +309,7 @@ void MatrixImpl::plan_exchange() {
 // MODE_SPLIT (NCCL send/recv + all-reduce) when IPC mapping is not possible on some rank.
 // -------------------------------------------------------------------------------------------------
 struct PeerBlob {
-    cudaIpcMemHandle_t buf[2], scal, flag;
+    cudaIpcMemHandle_t buf[kRing], scal, flag;
     int64_t halo_base;                 // nloc_pad: where the halo segment starts in the vector buffers
     int64_t peer_off[kMaxPeers + 1];   // offset of each owner's entries inside the halo segment
 };
@@ -303,14 +319,13 @@ void MatrixImpl::setup_peer() {
     if (nranks == 1) return;
     const char* want = std::getenv("EIGSOL_B200_EXCHANGE");
     const bool force_nccl = want && std::string(want) == "nccl";
-    d_scal_in.alloc(sizeof(double) * 2 * kMaxPeers * 4);
+    d_scal_in.alloc(sizeof(double) * kRing * kMaxPeers * 4);
     d_flag_in.alloc(sizeof(unsigned long long) * kMaxPeers);
     PeerBlob mine;
     std::memset(&mine, 0, sizeof mine);
     int ok = (nranks <= kMaxPeers && !force_nccl) ? 1 : 0;
     if (ok) {
-        ok &= cudaIpcGetMemHandle(&mine.buf[0], buf[0].p) == cudaSuccess;
-        ok &= cudaIpcGetMemHandle(&mine.buf[1], buf[1].p) == cudaSuccess;
+        for (int b = 0; b < kRing; ++b) ok &= cudaIpcGetMemHandle(&mine.buf[b], buf[b].p) == cudaSuccess;
         ok &= cudaIpcGetMemHandle(&mine.scal, d_scal_in.p) == cudaSuccess;
         ok &= cudaIpcGetMemHandle(&mine.flag, d_flag_in.p) == cudaSuccess;
         cudaGetLastError();
@@ -328,14 +343,13 @@ void MatrixImpl::setup_peer() {
     pa.flag_in = d_flag_in.as<unsigned long long>();
     pa.send_idx = d_send_idx.as<int32_t>();
     pa.spin_limit = (long long)env_int("EIGSOL_B200_PEER_TIMEOUT_MS", 4000) * 2000000LL;  // ~2 GHz ticks
-    pa.debug = env_int("EIGSOL_B200_PEER_DEBUG", 0);
     const size_t es = size_t(ss());
     int mapped = 1;
     for (int q = 0; q < nranks && mapped; ++q) {
         if (q == rank) continue;
         PeerBlob pb;
         std::memcpy(&pb, all.data() + sizeof(PeerBlob) * q, sizeof pb);
-        void* rb[2] = {nullptr, nullptr};
+        void* rb[kRing] = {nullptr, nullptr, nullptr};
         void *rs = nullptr, *rf = nullptr;
         auto open = [&](void** dst, const cudaIpcMemHandle_t& h) {
             if (cudaIpcOpenMemHandle(dst, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
@@ -345,8 +359,7 @@ void MatrixImpl::setup_peer() {
             }
             ipc_opened.push_back(*dst);
         };
-        open(&rb[0], pb.buf[0]);
-        if (mapped) open(&rb[1], pb.buf[1]);
+        for (int b = 0; b < kRing && mapped; ++b) open(&rb[b], pb.buf[b]);
         if (mapped) open(&rs, pb.scal);
         if (mapped) open(&rf, pb.flag);
         if (!mapped) break;
@@ -358,12 +371,12 @@ void MatrixImpl::setup_peer() {
             const int k = pa.nsend++;
             pa.send_start[k] = int(send_start[q]);
             pa.send_count[k] = int(send_count[q]);
-            for (int b = 0; b < 2; ++b) pa.send_dst[k][b] = static_cast<char*>(rb[b]) + dst_off;
+            for (int b = 0; b < kRing; ++b) pa.send_dst[k][b] = static_cast<char*>(rb[b]) + dst_off;
         } else {
             const int k = pa.nlist++;
             pa.list_off[k] = int(send_off[q]);
             pa.list_count[k] = int(send_count[q]);
-            for (int b = 0; b < 2; ++b) pa.list_dst[k][b] = static_cast<char*>(rb[b]) + dst_off;
+            for (int b = 0; b < kRing; ++b) pa.list_dst[k][b] = static_cast<char*>(rb[b]) + dst_off;
         }
     }
     mapped = comm_min_int(comm, mapped);
@@ -466,7 +479,8 @@ void MatrixImpl::set_kernel(int kernel_, int lanes_) {
         if (nblk == 0 && nloc > 0) {
             if (csr.rowptr.empty()) throw StateError("host CSR copy was released; row blocks cannot be rebuilt");
             const int tile = dtype ? StreamCfg<double2>::TILE : StreamCfg<double>::TILE;
-            std::vector<int32_t> rb = build_row_blocks(nloc, csr.rowptr.data(), tile, kStreamMaxRows);
+            rowblk_h = build_row_blocks(nloc, csr.rowptr.data(), tile, kStreamMaxRows);
+            const std::vector<int32_t>& rb = rowblk_h;
             nblk = int(rb.size()) - 1;
             d_rowblk.alloc(sizeof(int32_t) * rb.size());
             d_rowblk.upload(rb.data(), sizeof(int32_t) * rb.size(), stream);
@@ -566,7 +580,7 @@ void MatrixImpl::configure_launch() {
         const int target = sm_count * env_int("EIGSOL_B200_GEMV_WAVES", 4);
         nseg = std::max(1, target / ntiles);
         nseg = int(std::min<int64_t>(nseg, std::max<int64_t>(1, (ext_len + 31) / 32)));
-        grid = ntiles * nseg;
+        grid = ntiles * nseg + 1;  // + the control CTA
         nslots = ntiles;
         d_dense_partial.alloc(size_t(nseg) * size_t(lda) * size_t(s));
         d_tile_ticket.alloc(sizeof(unsigned) * size_t(ntiles));
@@ -581,61 +595,103 @@ void MatrixImpl::configure_launch() {
             case K_CSR_STREAM: need = nblk; break;
             case K_SELL: need = (sell_nslices + (block / 32) - 1) / (block / 32); break;
         }
-        grid = int(std::max<int64_t>(1, std::min<int64_t>(need, resident)));
-        nslots = grid;
+        // persistent grid: every CTA resident at once (the control CTA and the halo waits rely on it)
+        nslots = int(std::max<int64_t>(1, std::min<int64_t>(need, resident - 1)));
+        grid = nslots + 1;  // + the control CTA
         const int64_t xz = s * (nloc + nhalo) + s * nloc;
         if (kernel == K_SELL) stored_bytes = sell_padded * (s + 4) + 8 * (sell_nslices + 1) + xz;
         else stored_bytes = local_nnz * (s + 4) + 4 * (nloc + 1) + xz + (kernel == K_CSR_STREAM ? 4 * int64_t(nblk + 1) : 0);
     }
-    d_partials.alloc(sizeof(double) * 3 * size_t(nslots));
+    d_partials.alloc(sizeof(double) * 3 * size_t(nslots) * kRing);
+    build_deferred();
+}
+
+// MODE_PEER: which work units of the chosen kernel contain a row that reads a halo entry.  Those are
+// processed after the halo wait, everything else before it (kernels.cuh: walk_units).
+void MatrixImpl::build_deferred() {
+    have_deferred = false;
+    if (dense || xmode != MODE_PEER || nhalo == 0 || csr.rowptr.empty()) return;
+    int64_t nunits = 0;
+    auto unit_of_row = [&](int64_t r) -> int64_t { return r; };
+    (void)unit_of_row;
+    std::vector<int64_t> unit_first;  // first row of each unit (+ end)
+    switch (kernel) {
+        case K_CSR_SCALAR: nunits = (nloc + block - 1) / block; break;
+        case K_CSR_VECTOR: nunits = (nloc + (block / lanes) - 1) / (block / lanes); break;
+        case K_CSR_STREAM: nunits = nblk; break;
+        case K_SELL: nunits = sell_nslices; break;
+        default: return;
+    }
+    std::vector<uint8_t> def(size_t(std::max<int64_t>(nunits, 1)), 0);
+    auto row_reads_halo = [&](int64_t r) {
+        for (int32_t p = csr.rowptr[size_t(r)]; p < csr.rowptr[size_t(r) + 1]; ++p)
+            if (csr.colidx[size_t(p)] >= nloc_pad) return true;
+        return false;
+    };
+    for (int64_t u = 0; u < nunits; ++u) {
+        int64_t r0, r1;
+        switch (kernel) {
+            case K_CSR_SCALAR: r0 = u * block; r1 = r0 + block; break;
+            case K_CSR_VECTOR: r0 = u * (block / lanes); r1 = r0 + block / lanes; break;
+            case K_CSR_STREAM: r0 = rowblk_h[size_t(u)]; r1 = rowblk_h[size_t(u) + 1]; break;
+            default: r0 = u * 32 * sell_R; r1 = r0 + 32 * sell_R; break;
+        }
+        r1 = std::min<int64_t>(r1, nloc);
+        for (int64_t r = r0; r < r1 && !def[size_t(u)]; ++r)
+            if (row_reads_halo(r)) def[size_t(u)] = 1;
+    }
+    d_deferred.alloc(def.size());
+    d_deferred.upload(def.data(), def.size(), stream);
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    have_deferred = true;
 }
 
 // One matvec launch on `stream`.  All launches of a handle are identical (the kernels pick the
 // ping-pong buffer from the device state), which is what lets a CUDA graph of them be replayed.
-template <class S> static void launch_sparse(MatrixImpl& m) {
+template <class S> static void launch_sparse(MatrixImpl& m, int ph) {
     constexpr int B = 256;
     IterArgs<S> it = m.iter_args<S>();
     CsrView<S> A{int32_t(m.nloc), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
     const dim3 g(m.grid), b(B);
     cudaStream_t st = m.stream;
     switch (m.kernel) {
-        case K_CSR_SCALAR: spmv_csr_scalar_kernel<S, B><<<g, b, 0, st>>>(A, it); break;
-        case K_CSR_STREAM: spmv_csr_stream_kernel<S, B><<<g, b, 0, st>>>(A, m.d_rowblk.as<int32_t>(), m.nblk, it); break;
+        case K_CSR_SCALAR: spmv_csr_scalar_kernel<S, B><<<g, b, 0, st>>>(A, it, ph); break;
+        case K_CSR_STREAM: spmv_csr_stream_kernel<S, B><<<g, b, 0, st>>>(A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
         case K_SELL: {
             SellView<S> V{int32_t(m.nloc), int32_t(m.sell_nslices), m.d_sell_off.as<int64_t>(), m.d_sell_col.as<int32_t>(),
                           m.d_sell_val.as<S>()};
-            if (m.lanes == 2) spmv_sell_kernel<S, 2, B><<<g, b, 0, st>>>(V, it);
-            else spmv_sell_kernel<S, 1, B><<<g, b, 0, st>>>(V, it);
+            if (m.lanes == 2) spmv_sell_kernel<S, 2, B><<<g, b, 0, st>>>(V, it, ph);
+            else spmv_sell_kernel<S, 1, B><<<g, b, 0, st>>>(V, it, ph);
             break;
         }
         case K_CSR_VECTOR:
             switch (m.lanes) {
-                case 2: spmv_csr_vector_kernel<S, 2, B><<<g, b, 0, st>>>(A, it); break;
-                case 4: spmv_csr_vector_kernel<S, 4, B><<<g, b, 0, st>>>(A, it); break;
-                case 8: spmv_csr_vector_kernel<S, 8, B><<<g, b, 0, st>>>(A, it); break;
-                case 16: spmv_csr_vector_kernel<S, 16, B><<<g, b, 0, st>>>(A, it); break;
-                default: spmv_csr_vector_kernel<S, 32, B><<<g, b, 0, st>>>(A, it); break;
+                case 2: spmv_csr_vector_kernel<S, 2, B><<<g, b, 0, st>>>(A, it, ph); break;
+                case 4: spmv_csr_vector_kernel<S, 4, B><<<g, b, 0, st>>>(A, it, ph); break;
+                case 8: spmv_csr_vector_kernel<S, 8, B><<<g, b, 0, st>>>(A, it, ph); break;
+                case 16: spmv_csr_vector_kernel<S, 16, B><<<g, b, 0, st>>>(A, it, ph); break;
+                default: spmv_csr_vector_kernel<S, 32, B><<<g, b, 0, st>>>(A, it, ph); break;
             }
             break;
         default: throw StateError("no sparse kernel selected");
     }
 }
 
-template <class S> static void launch_dense(MatrixImpl& m) {
+template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     constexpr int B = 256;
     IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
-    gemv_colmajor_kernel<S, B><<<dim3(m.grid), dim3(B), 0, m.stream>>>(A, it);
+    gemv_colmajor_kernel<S, B><<<dim3(m.grid), dim3(B), 0, m.stream>>>(A, it, ph);
 }
 
-void MatrixImpl::launch_matvec() {
+void MatrixImpl::launch_matvec(int phase) {
     if (dense) {
-        if (dtype) launch_dense<double2>(*this);
-        else launch_dense<double>(*this);
+        if (dtype) launch_dense<double2>(*this, phase);
+        else launch_dense<double>(*this, phase);
     } else {
-        if (dtype) launch_sparse<double2>(*this);
-        else launch_sparse<double>(*this);
+        if (dtype) launch_sparse<double2>(*this, phase);
+        else launch_sparse<double>(*this, phase);
     }
     ++launches;
 }
@@ -649,12 +705,17 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol) {
     PowerState st;
     std::memset(&st, 0, sizeof st);
     st.q[0] = 1.0;  // x0 arrives normalised (power_method.hpp:62); launch 0 uses it as is
-    st.q[1] = 0.0;
+    st.sigma[0] = 1.0;
     st.tol = tol;
     st.final_q = 1.0;
     st.max_trips = max_it;
     st.stop = max_it <= 0 ? STOP_MAX_TRIPS : STOP_NONE;  // the loop of :68 never runs
+    st.ctrl[0].sigma = 1.0;
+    st.ctrl[0].launch_no = 0;
+    st.ctrl[0].active = max_it > 0 ? 1 : 0;
     max_trips = max_it;
+    flag_epoch += (unsigned long long)issued + 1;  // flags are monotonic across solves: stale late stores stay below
+    st.flag_base = flag_epoch;
     issued = 0;
     const size_t s = size_t(ss());
     EIGSOL_CUDA(cudaMemcpyAsync(d_state.p, &st, sizeof st, cudaMemcpyHostToDevice, stream));
@@ -673,10 +734,6 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol) {
                                         cudaMemcpyHostToDevice, stream));
             EIGSOL_CUDA(cudaStreamSynchronize(stream));
         }
-        if (xmode == MODE_PEER) {
-            EIGSOL_CUDA(cudaMemsetAsync(d_scal_in.p, 0, d_scal_in.bytes, stream));
-            EIGSOL_CUDA(cudaMemsetAsync(d_flag_in.p, 0, d_flag_in.bytes, stream));
-        }
         // barrier: no rank may start launching (and storing into peers) before every rank has reset
         EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 1, ncclDouble, ncclSum, comm->nccl_comm, stream));
     }
@@ -687,7 +744,7 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol) {
 // x exchange of the multi-GPU path: every rank sends the entries its peers' rows reference and
 // receives its own halo (semantically the all-gather of x; only the referenced entries move).
 template <class S> static void exchange_impl(MatrixImpl& m, int in) {
-    S* u = m.buf[in].as<S>();
+    S* u = m.buf[in].as<S>();  // in = launch number % kRing
     const int ncclT = ncclDouble;
     const size_t mul = sizeof(S) / sizeof(double);
     if (m.need_pack) {
@@ -724,14 +781,21 @@ void MatrixImpl::issue_trips(int k) {
     if (k <= 0) return;
     EIGSOL_CUDA(cudaSetDevice(device));
     if (xmode != MODE_SPLIT) {
-        const int glen = env_int("EIGSOL_B200_GRAPH", 16);
-        if (glen > 1 && k >= glen) {
+        // a CUDA graph of glen launches (a multiple of kRing, so every node's ring phase is fixed)
+        int glen = env_int("EIGSOL_B200_GRAPH", 15);
+        glen = glen / kRing * kRing;
+        while (k > 0 && (issued % kRing != 0 || k < glen || glen < kRing)) {
+            launch_matvec(issued % kRing);
+            ++issued;
+            --k;
+        }
+        if (k >= glen && glen >= kRing) {
             if (!graph || graph_len != glen) {
                 drop_graph();
                 cudaGraph_t g = nullptr;
                 EIGSOL_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
                 const int64_t keep = launches;
-                for (int i = 0; i < glen; ++i) launch_matvec();
+                for (int i = 0; i < glen; ++i) launch_matvec(i % kRing);
                 launches = keep;
                 EIGSOL_CUDA(cudaStreamEndCapture(stream, &g));
                 EIGSOL_CUDA(cudaGraphInstantiate(&graph, g, 0));
@@ -745,33 +809,33 @@ void MatrixImpl::issue_trips(int k) {
                 k -= glen;
             }
         }
-        for (int i = 0; i < k; ++i) {
-            launch_matvec();
+        for (; k > 0; --k) {
+            launch_matvec(issued % kRing);
             ++issued;
         }
         EIGSOL_CUDA(cudaGetLastError());
         return;
     }
+    // MODE_SPLIT (NCCL): halo send/recv -> matvec (its control CTA folds the all-reduced sums of the previous
+    // launch) -> fixed-order sum of the CTA partials -> all-reduce of 3 doubles
     for (int i = 0; i < k; ++i) {
-        exchange_halo(issued & 1);
-        launch_matvec();
-        reduce_partials_kernel<256><<<1, 256, 0, stream>>>(d_partials.as<double>(), nslots, d_state.as<PowerState>(),
-                                                          d_scal.as<double>());
-        EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 3, ncclDouble, ncclSum, comm->nccl_comm, stream));
-        finalize_kernel<<<1, 32, 0, stream>>>(d_state.as<PowerState>(), d_scal.as<double>());
-        launches += 2;
+        const int ph = issued % kRing;
+        if (issued > 0) exchange_halo(ph);  // the halo of launch 0 came from the host's x0
+        launch_matvec(ph);
+        double* sc = d_scal.as<double>() + 4 * ph;
+        reduce_partials_kernel<256><<<1, 256, 0, stream>>>(d_partials.as<double>() + size_t(ph) * size_t(nslots) * 3, nslots, sc);
+        EIGSOL_NCCL(nccl().AllReduce(sc, sc, 3, ncclDouble, ncclSum, comm->nccl_comm, stream));
+        launches += 1;
         ++issued;
     }
     EIGSOL_CUDA(cudaGetLastError());
 }
 
 const PowerState& MatrixImpl::poll_state() {
-    if (xmode == MODE_PEER) {
-        // fold the sums of the last executed launch into the state (waits for the peers' flags)
-        if (dtype) peer_flush_kernel<double2><<<1, 32, 0, stream>>>(iter_args<double2>());
-        else peer_flush_kernel<double><<<1, 32, 0, stream>>>(iter_args<double>());
-        ++launches;
-    }
+    // fold the sums of the last executed launch into the state (MODE_PEER: exchanges them with the peers)
+    if (dtype) control_kernel<double2><<<1, 256, 0, stream>>>(iter_args<double2>());
+    else control_kernel<double><<<1, 256, 0, stream>>>(iter_args<double>());
+    ++launches;
     EIGSOL_CUDA(cudaMemcpyAsync(h_state.p, d_state.p, sizeof(PowerState), cudaMemcpyDeviceToHost, stream));
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
     if (h_state.as<PowerState>()->stop == STOP_ERROR)
@@ -819,10 +883,10 @@ void MatrixImpl::end(void* x_out, double lambda_out[2], int* iters, int* conv) {
     if (x_out) {
         const int g = int(std::max<int64_t>(1, std::min<int64_t>((nloc + 255) / 256, sm_count * 8)));
         if (dtype)
-            normalize_result_kernel<double2><<<g, 256, 0, stream>>>(buf[0].as<double2>(), buf[1].as<double2>(),
+            normalize_result_kernel<double2><<<g, 256, 0, stream>>>(buf[0].as<double2>(), buf[1].as<double2>(), buf[2].as<double2>(),
                                                                    d_state.as<PowerState>(), d_xloc.as<double2>(), int(nloc));
         else
-            normalize_result_kernel<double><<<g, 256, 0, stream>>>(buf[0].as<double>(), buf[1].as<double>(),
+            normalize_result_kernel<double><<<g, 256, 0, stream>>>(buf[0].as<double>(), buf[1].as<double>(), buf[2].as<double>(),
                                                                   d_state.as<PowerState>(), d_xloc.as<double>(), int(nloc));
         ++launches;
         EIGSOL_CUDA(cudaGetLastError());
@@ -837,8 +901,8 @@ void MatrixImpl::end(void* x_out, double lambda_out[2], int* iters, int* conv) {
 }
 
 // Whole solve: power_method.hpp:61-98.  maxIterations trips need maxIterations+1 launches (launch 0
-// is y = A x0 of trip 0; launch l >= 1 closes trip l-1).  The host polls the device state between
-// batches; launches issued past the stopping point are no-ops on the device.
+// is y = A x0 of trip 0; the sums of launch l >= 1 close trip l-1; the poll folds the last ones).  The
+// host polls the device state between batches; launches issued past the stopping point are no-ops.
 void MatrixImpl::run(const void* x0, int max_it, double tol, void* x_out, double lambda_out[2], int* iters, int* conv) {
     begin(x0, max_it, tol);
     if (max_it > 0) {
@@ -888,7 +952,7 @@ void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
     info->rank = rank;
     int per_trip = 1;
     if (xmode == MODE_SPLIT) {
-        per_trip += 2;
+        per_trip += 1;
         for (int q = 0; q < nranks; ++q)
             if (send_count[q] > 0 && !send_contig[q]) ++per_trip;
     }

@@ -1,14 +1,15 @@
 // kernels.cuh -- hand-written sm_100a kernels of the power-iteration path.
 //
-// One launch == one power iteration's matvec with everything else fused into it:
-//     x  = u / ||u||                 (reference: src/power_method/power_method.hpp:72,78)
-//     z  = A x                       (:69 of the NEXT trip == the A*x temporary of :81, computed once)
-//     d  = x^H z  (conjugated dot)   (:81, eigen/Eigen/src/Core/InnerProduct.h:255)
-//     q' = ||z||^2                   (:72 of the next trip, eigen/Eigen/src/Core/Dot.h:61-77)
-// and, on one GPU, the convergence test of :83-95 (src/core/tolerance.hpp:28-33) in the last CTA to
-// finish.  u is the un-normalised output of the previous launch; x is never written to HBM, so an
-// iteration reads A once, reads u once (gathers served from L1/L2), writes z once: exactly the
-// algorithmic bytes of SURVEY.md 8(d).
+// One launch == one power iteration's matvec with everything else fused into it or overlapped with it:
+//     v' = sigma * A v               (reference: src/power_method/power_method.hpp:69; the A*x temporary of
+//                                     :81 is the next trip's y, computed once; sigma = power-of-two scale)
+//     a  = v^H v'  (conjugated dot)  (:81, eigen/Eigen/src/Core/InnerProduct.h:255)
+//     q' = ||v'||^2                  (:72 of the next trip, eigen/Eigen/src/Core/Dot.h:61-77)
+// and, one launch later and in parallel with that launch's matvec CTAs, the Rayleigh quotient,
+// the convergence test of :83-95 (src/core/tolerance.hpp:28-33) and -- on N GPUs -- the all-reduce of
+// (a, q') in the launch's control CTA.  The normalised x is never written to HBM, so an iteration reads
+// A once, reads v once (gathers served from L1/L2), writes v' once: exactly the algorithmic bytes of
+// SURVEY.md 8(d).
 //
 // Bandwidth-bound integer/fp64 streaming work: no tensor cores.  What matters here is coalescing
 // (128-bit loads of values / column indices), enough bytes in flight per SM, a persistent grid sized
@@ -18,30 +19,6 @@
 #include <stdint.h>
 
 namespace eigsol_b200 {
-
-// -------------------------------------------------------------------------------------------------
-// Device-resident iteration state (one per matrix handle).  Mirrors the locals of powerMethodImpl
-// (power_method.hpp:61-66): lambda, usedIters, converged, initialized.
-// -------------------------------------------------------------------------------------------------
-struct PowerState {
-    double q[2];        // ||u||^2 of ping-pong buffer 0 / 1
-    double lambda[2];   // current eigenvalue estimate (re, im)
-    double tol;         // opts.tolerance
-    double final_q;     // ||u||^2 of the buffer holding the result vector
-    int max_trips;      // opts.maxIterations
-    int launches;       // effective launches done; buffer (launches & 1) is the next input
-    int trips;          // usedIters
-    int initialized;    // power_method.hpp:66
-    int stop;           // 0 running, 1 converged, 2 zero norm (:73-76), 3 maxIterations reached
-    int converged;
-    int final_buf;      // buffer whose normalisation is EigenResult::eigenvector
-    unsigned ticket;    // CTA completion counter of the running launch
-    int pending;        // MODE_PEER: launch `launches` has run but its global sums are not folded in yet
-    int reserved;
-};
-
-enum { STOP_NONE = 0, STOP_CONVERGED = 1, STOP_ZERO_NORM = 2, STOP_MAX_TRIPS = 3,
-       STOP_ERROR = 4 };  // a peer never signalled (MODE_PEER wait timed out)
 
 // -------------------------------------------------------------------------------------------------
 // Scalar traits: double and complex<double> (as double2 = interleaved re, im).
@@ -158,50 +135,56 @@ template <class S> struct DenseView {
     unsigned* tile_ticket;  // [ntiles]
 };
 
-// How the grid-level finish of a launch is done.
-enum { MODE_FUSED = 0,   // one GPU: the last CTA sums the partials and runs the convergence test
-       MODE_SPLIT = 1,   // N GPUs over NCCL: partials only; reduce + all-reduce + finalize_kernel follow
-       MODE_PEER = 2 };  // N GPUs over peer memory: ONE kernel per iteration does matvec + x exchange +
-                         // scalar all-reduce (P2P stores over NVLink, flags with system-scope release/acquire)
+// -------------------------------------------------------------------------------------------------
+// Device-resident iteration state (one per matrix handle).  Mirrors the locals of powerMethodImpl
+// (power_method.hpp:61-66): lambda, usedIters, converged, initialized.
+//
+// Pipeline.  Launch m reads the vector v_m (ring buffer m % 3) and writes v_{m+1} = sigma_m * A v_m into
+// buffer (m+1) % 3; every matvec CTA leaves three partial sums
+//     a_m = v_m^H (sigma_m A v_m)      (re, im)          q_{m+1} = ||v_{m+1}||^2
+// in its slot and exits -- no atomics, no fences, no "last CTA".  CTA 0 of every launch is the CONTROL
+// CTA: while the other CTAs of launch m stream the matrix, it folds the sums of launch m-1 into the state
+// (on N GPUs: publishes them to every peer and adds the peers' sums in rank order), closes trip m-2 of
+// power_method.hpp:68-96
+//     lambda = a_{m-1} / (sigma_{m-1} q_{m-1})   ( = x^H A x with x = v_{m-1}/||v_{m-1}|| , :81 )
+//     convergence test (:83-91), maxIterations, ||y|| == 0 exit (:73-76)
+// and writes the control record of launch m+1 (scale, active flag).  So the scalar reduction, the
+// cross-GPU all-reduce and the state transition are OFF the critical path: they overlap a whole matvec.
+// The scale sigma is a power of two chosen from the norms seen two launches ago, so the stored vector
+// stays O(1) and the scaling itself is exact; the Rayleigh quotient is scale-invariant and the returned
+// eigenvector is normalised by a true division at the end (:78).  Three buffers keep the vector of the
+// stopping trip intact while the (at most one) launch already in flight completes.
+// -------------------------------------------------------------------------------------------------
+constexpr int kRing = 3;
 
-constexpr int kMaxPeers = 8;
-
-// Multi-GPU peer-memory wiring of one rank (MODE_PEER).  Every rank runs the same launch sequence in
-// lock step: launch l reads buffer l&1 (own rows + halo) and writes buffer (l+1)&1.  Rows of z that a
-// peer's rows reference are ALSO stored straight into that peer's halo region of ITS buffer (l+1)&1,
-// the rank's three partial sums go to every peer's scal_in[l&1][rank], and finally flag_in[rank] on every
-// peer is set to l+1 (release).  Launch l+1 starts by waiting for all its flag_in[q] >= l+1 (acquire).
-struct PeerArgs {
-    int nranks, rank;
-    int nsend;                        // contiguous send ranges (rows stored remotely as they are produced)
-    int send_start[kMaxPeers];        // first local row of the range
-    int send_count[kMaxPeers];
-    void* send_dst[kMaxPeers][2];     // remote address of the peer's halo segment, per buffer parity
-    int nlist;                        // scattered send lists (copied by the last CTA)
-    int list_off[kMaxPeers], list_count[kMaxPeers];
-    void* list_dst[kMaxPeers][2];
-    const int32_t* send_idx;          // local row indices of the scattered lists
-    double* peer_scal[kMaxPeers];     // remote scal_in base of rank q (nullptr for self)
-    unsigned long long* peer_flag[kMaxPeers];  // remote &flag_in[rank] of rank q
-    double* scal_in;                  // local [2][kMaxPeers][4]
-    unsigned long long* flag_in;      // local [kMaxPeers]
-    long long spin_limit;             // clock64 ticks before a wait gives up (STOP_ERROR)
-    int debug;                        // TIMING EXPERIMENTS ONLY (EIGSOL_B200_PEER_DEBUG): 1 no sys fence per CTA, 2 no halo stores, 4 no wait, 8 no publish
+struct LaunchCtrl {
+    double sigma;   // v_{m+1} = sigma * A v_m
+    int launch_no;  // m
+    int active;     // 0: the launch is a no-op (stopped, or past maxIterations)
 };
 
-// Everything a matvec launch needs besides the matrix.
-template <class S> struct IterArgs {
-    S* buf0;             // ping-pong vector buffers, extended layout [local | halo]
-    S* buf1;
-    PowerState* st;
-    double* partials;    // 3 doubles per CTA slot: d_re, d_im, q'
-    int mode;            // MODE_*
-    const PeerArgs* peer;  // device copy (MODE_PEER), else nullptr
+struct PowerState {
+    double lambda[2];      // current eigenvalue estimate (re, im)
+    double tol;            // opts.tolerance
+    double q[kRing];       // ||v_m||^2 at slot m % 3
+    double sigma[kRing];   // sigma_m at slot m % 3
+    double final_q;        // ||v||^2 of the buffer holding the result vector
+    unsigned long long flag_base;  // peer flags of this solve are flag_base + launch number (never reset: monotonic)
+    int max_trips;         // opts.maxIterations
+    int launch_no;         // launches executed since begin (the next launch is number launch_no)
+    int folded;            // launches whose sums have been folded into the state
+    int trips;             // usedIters
+    int initialized;       // power_method.hpp:66
+    int stop;              // STOP_*
+    int converged;
+    int final_buf;         // ring buffer whose normalisation is EigenResult::eigenvector
+    int error;             // a peer never signalled (wait timed out)
+    int reserved;
+    LaunchCtrl ctrl[kRing];  // control record of launch m at slot m % 3
 };
 
-// -------------------------------------------------------------------------------------------------
-// State transitions.
-// -------------------------------------------------------------------------------------------------
+enum { STOP_NONE = 0, STOP_CONVERGED = 1, STOP_ZERO_NORM = 2, STOP_MAX_TRIPS = 3, STOP_ERROR = 4 };
+
 // tolerance.hpp:28-33 with a = lambdaNew, b = lambda: |a-b| <= tol*(1+|a|), |.| the complex modulus.
 __device__ __forceinline__ bool close_relative(double are, double aim, double bre, double bim, double tol) {
     const double diff = hypot(are - bre, aim - bim);
@@ -209,39 +192,99 @@ __device__ __forceinline__ bool close_relative(double are, double aim, double br
     return diff <= tol * scale;
 }
 
-// Runs once per effective launch l, after the global sums (d_re, d_im, q') of that launch are known.
-// Launch l consumed u_l (buffer in = l & 1, squared norm qin) and produced u_{l+1}.  For l >= 1 the
-// sums are trip k = l-1 of power_method.hpp:68-96: lambdaNew = d, and x_{k+1} = u_l / sqrt(qin).
-__device__ __forceinline__ void finalize_launch(PowerState* st, double dre, double dim, double qn, int l, int in,
-                                                double qin) {
-    st->q[in ^ 1] = qn;
-    if (l >= 1) {
-        const bool close = st->initialized && close_relative(dre, dim, st->lambda[0], st->lambda[1], st->tol);
-        st->lambda[0] = dre;
-        st->lambda[1] = dim;
-        st->trips = l;
-        st->final_buf = in;
-        st->final_q = qin;
+// Folds the global sums of launch j (a = v_j^H z, qn = ||v_{j+1}||^2) into the state.  For j >= 1 this
+// closes trip k = j-1 of power_method.hpp:68-96: x_{k+1} = v_j / ||v_j|| and lambdaNew = x^H A x.
+__device__ __forceinline__ void fold_launch(PowerState* st, int j, double are, double aim, double qn) {
+    const int r = j % kRing;
+    st->q[(j + 1) % kRing] = qn;
+    if (j >= 1) {
+        const double denom = st->sigma[r] * st->q[r];
+        const double lre = are / denom, lim = aim / denom;
+        const bool close = st->initialized && close_relative(lre, lim, st->lambda[0], st->lambda[1], st->tol);
+        st->lambda[0] = lre;
+        st->lambda[1] = lim;
+        st->trips = j;
+        st->final_buf = r;
+        st->final_q = st->q[r];
         st->initialized = 1;
         if (close) {
             st->converged = 1;
             st->stop = STOP_CONVERGED;
-        } else if (l >= st->max_trips) {
+        } else if (j >= st->max_trips) {
             st->stop = STOP_MAX_TRIPS;
         }
     }
-    st->launches = l + 1;
-    st->ticket = 0;
+    if (st->stop == STOP_NONE && qn == 0.0) {
+        // trip j found normY == 0 (power_method.hpp:73-76): x and lambda stay those of the previous
+        // trip, usedIters = j+1.
+        st->trips = j + 1;
+        st->final_buf = r;
+        st->final_q = st->q[r];
+        st->stop = STOP_ZERO_NORM;
+    }
+    st->folded = j + 1;
 }
 
-// trip k = l-1 found normY == 0 (power_method.hpp:73-76): x and lambda stay those of the previous
-// trip, usedIters = k+1.
-__device__ __forceinline__ void zero_norm_stop(PowerState* st, int l, int in) {
-    st->trips = l;
-    st->final_buf = in ^ 1;
-    st->final_q = st->q[in ^ 1];
-    st->stop = STOP_ZERO_NORM;
+// Scale of launch m+1, from what is known after folding launch m-1: growth^2 g2 = ||A v||^2/||v||^2 seen
+// in launch m-1 and the predicted ||v_{m+1}||^2 = sigma_m^2 g2 q_m.  Rounded to a power of two.
+__device__ __forceinline__ double next_sigma(const PowerState* st, int m) {
+    if (m == 0) return 1.0;
+    const int r = m % kRing, p = (m - 1) % kRing;
+    const double qm = st->q[r], qp = st->q[p], sm = st->sigma[r], sp = st->sigma[p];
+    const double g2 = qm / (sp * sp * qp);
+    const double pred2 = sm * sm * g2 * qm;
+    const double x = g2 * pred2;
+    if (!(x > 0.0) || !isfinite(x)) return 1.0;
+    const int k = int(rint(0.5 * log2(x)));
+    if (k > 900 || k < -900) return 1.0;
+    return ldexp(1.0, -k);
 }
+
+// How the sums of a launch become global and how the halo of x travels.
+enum { MODE_FUSED = 0,   // one GPU
+       MODE_SPLIT = 1,   // N GPUs over NCCL: send/recv of the halo before, all-reduce of the sums after each launch
+       MODE_PEER = 2 };  // N GPUs over peer memory: the matvec kernel itself stores boundary rows into the peers'
+                         // halo segments and the control CTA exchanges the sums (P2P stores over NVLink, flags with
+                         // system-scope release/acquire)
+
+constexpr int kMaxPeers = 8;
+
+// Multi-GPU peer-memory wiring of one rank (MODE_PEER).  Launch m reads ring buffer m%3 (own rows + halo)
+// and writes (m+1)%3.  Rows of v_{m+1} that a peer's rows reference are ALSO stored straight into that
+// peer's halo segment of ITS buffer (m+1)%3 as they are produced.  The control CTA of launch m+1 then
+// writes this rank's sums of launch m into every peer's scal_in[m%3][rank] and sets flag_in[rank] = m+1
+// on every peer (release): "my launches <= m are complete -- your halo of v_{m+1} has landed -- and my
+// sums of launch m are in your mailbox".  A peer's launch m+1 processes the rows that read halo entries
+// LAST and waits for the flag (acquire) only before those, so the exchange overlaps its interior rows.
+struct PeerArgs {
+    int nranks, rank;
+    int nsend;                        // contiguous send ranges (rows stored remotely as they are produced)
+    int send_start[kMaxPeers];        // first local row of the range
+    int send_count[kMaxPeers];
+    void* send_dst[kMaxPeers][kRing]; // remote address of the peer's halo segment, per ring buffer
+    int nlist;                        // scattered send lists (copied by the next launch's control CTA)
+    int list_off[kMaxPeers], list_count[kMaxPeers];
+    void* list_dst[kMaxPeers][kRing];
+    const int32_t* send_idx;          // local row indices of the scattered lists
+    double* peer_scal[kMaxPeers];     // remote scal_in base of rank q (nullptr for self)
+    unsigned long long* peer_flag[kMaxPeers];  // remote &flag_in[rank] of rank q
+    double* scal_in;                  // local [kRing][kMaxPeers][4]
+    unsigned long long* flag_in;      // local [kMaxPeers]
+    long long spin_limit;             // clock64 ticks before a wait gives up (error -> STOP_ERROR)
+};
+
+// Everything a matvec launch needs besides the matrix.
+template <class S> struct IterArgs {
+    S* buf[kRing];           // ring of vector buffers, extended layout [local | halo]
+    PowerState* st;
+    double* partials;        // [kRing][nslots][3]: a_re, a_im, q' per matvec CTA (or GEMV row tile)
+    int nslots;
+    int mode;                // MODE_*
+    const PeerArgs* peer;    // device copy (MODE_PEER), else nullptr
+    const double* scal_glob; // MODE_SPLIT: [kRing][4] all-reduced sums of launch j at slot j%3
+    const uint8_t* deferred; // MODE_PEER: per work unit, 1 = reads halo entries (done after the halo wait); may be null
+    int serpentine;          // odd launches walk the work units backwards (what was touched last is re-read first: L2)
+};
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
     unsigned long long v;
@@ -257,17 +300,16 @@ __device__ __forceinline__ double ld_volatile_f64(const double* p) {
     return v;
 }
 
-// Per-launch context (kept small: it lives in registers across the matvec loop).  The state AFTER
-// everything a launch learns in its prologue (the deferred finalize of the previous launch in MODE_PEER,
-// a zero-norm stop) is a pure function of the state in memory and the peers' sums, so every thread of
-// every CTA derives the same decision, and the last CTA to finish re-derives the full state and is the
-// only one that writes it back: no CTA ever reads a half-updated state.
-struct LaunchCtx {
-    int l, in;
-    double qin, s;
-    int dirty;    // the derived state differs from the state in memory
-    int wait_ok;  // MODE_PEER: every peer signalled in time
-};
+// Spins (one thread) until every peer's flag has reached `want`; false on timeout.
+__device__ __forceinline__ bool wait_peer_flags(const PeerArgs& pa, unsigned long long want) {
+    const long long t0 = clock64();
+    for (int q = 0; q < pa.nranks; ++q) {
+        if (q == pa.rank) continue;
+        while (ld_acquire_sys(pa.flag_in + q) < want)
+            if (clock64() - t0 > pa.spin_limit) return false;
+    }
+    return true;
+}
 
 // -------------------------------------------------------------------------------------------------
 // CTA reduction of the three running sums.  Deterministic: fixed shuffle tree inside the CTA.
@@ -302,184 +344,205 @@ __device__ __forceinline__ void cta_sum3(double& a, double& b, double& c, double
 }
 
 // -------------------------------------------------------------------------------------------------
-// Per-launch prologue, executed by every thread: returns false when the launch must be a no-op
-// (already stopped, past maxIterations, ||y|| == 0, or a peer wait timed out).
-// MODE_PEER: first wait until every peer has finished the previous launch (its halo rows and partial
-// sums have landed here), add the partial sums in rank order and run the deferred finalize.
+// The control CTA: blockIdx.x == 0 of every matvec launch (advance = true), and the whole of
+// control_kernel (advance = false: folds what is pending so the host reads a settled state).
+// Control CTAs are the only writers of the state and are ordered by the stream.
 // -------------------------------------------------------------------------------------------------
-// Derives (ns, c) from the state in memory; returns true when the launch is active.  No barriers.
-template <class S>
-__device__ __noinline__ bool derive_state(const IterArgs<S>& it, PowerState& ns, LaunchCtx& c) {
-    ns = *it.st;
-    c.dirty = 0;
-    if (ns.stop != STOP_NONE) return false;
-    if (it.mode == MODE_PEER && ns.pending) {
+template <class S, int BLOCK>
+__device__ void control_cta(const IterArgs<S>& it, bool advance) {
+    __shared__ double sred[3][BLOCK / 32];
+    PowerState* st = it.st;
+    const int m = st->launch_no;
+    const int j = m - 1;  // the launch whose sums are folded now
+    const unsigned long long flagv = st->flag_base + (unsigned long long)m;
+    const bool have = j >= 0 && st->folded == j;
+    const bool fold = have && st->ctrl[(j + kRing) % kRing].active && st->stop == STOP_NONE && !st->error;
+    double a = 0.0, b = 0.0, d = 0.0;
+    if (fold) {
+        const double* part = it.partials + size_t(j % kRing) * size_t(it.nslots) * 3;
+        for (int i = threadIdx.x; i < it.nslots; i += BLOCK) {
+            a += __ldcg(part + 3 * i + 0);
+            b += __ldcg(part + 3 * i + 1);
+            d += __ldcg(part + 3 * i + 2);
+        }
+    }
+    cta_sum3<BLOCK>(a, b, d, sred);
+    if (it.mode == MODE_PEER && fold) {
+        // scattered send lists: rows of v_m the peers' rows reference, copied into their halo segments
         const PeerArgs& pa = *it.peer;
-        const int lp = ns.launches;  // executed, not yet finalized
-        c.dirty = 1;
-        if (!c.wait_ok) {
-            ns.stop = STOP_ERROR;
-            return false;
+        const S* v = it.buf[m % kRing];
+        for (int k = 0; k < pa.nlist; ++k) {
+            S* dst = static_cast<S*>(pa.list_dst[k][m % kRing]);
+            const int32_t* idx = pa.send_idx + pa.list_off[k];
+            for (int i = threadIdx.x; i < pa.list_count[k]; i += BLOCK) dst[i] = Sc<S>::ldcg(v + idx[i]);
         }
-        double a = 0.0, b = 0.0, d = 0.0;
-        const double* sc = pa.scal_in + (lp & 1) * kMaxPeers * 4;
-        for (int q = 0; q < pa.nranks; ++q) {
-            a += ld_volatile_f64(sc + 4 * q + 0);
-            b += ld_volatile_f64(sc + 4 * q + 1);
-            d += ld_volatile_f64(sc + 4 * q + 2);
-        }
-        finalize_launch(&ns, a, b, d, lp, lp & 1, ns.q[lp & 1]);
-        ns.pending = 0;
-        if (ns.stop != STOP_NONE) return false;
+        if (pa.nlist) __threadfence_system();
     }
-    c.l = ns.launches;
-    if (c.l > ns.max_trips) return false;
-    c.in = c.l & 1;
-    c.qin = ns.q[c.in];
-    if (c.qin == 0.0) {
-        if (it.mode != MODE_SPLIT) {  // MODE_SPLIT: finalize_kernel takes the decision
-            zero_norm_stop(&ns, c.l, c.in);
-            c.dirty = 1;
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    int ok = 1;
+    if (it.mode == MODE_PEER) {
+        const PeerArgs& pa = *it.peer;
+        if (fold) {
+            const int slot = (j % kRing) * kMaxPeers * 4 + pa.rank * 4;
+            pa.scal_in[slot + 0] = a;
+            pa.scal_in[slot + 1] = b;
+            pa.scal_in[slot + 2] = d;
+            for (int q = 0; q < pa.nranks; ++q) {
+                if (q == pa.rank) continue;
+                double* dst = pa.peer_scal[q] + slot;
+                dst[0] = a;
+                dst[1] = b;
+                dst[2] = d;
+            }
         }
-        return false;
+        // "my launches < m are complete (your halo of v_m has landed) and my sums of launch m-1 are with you"
+        for (int q = 0; q < pa.nranks; ++q)
+            if (q != pa.rank) st_release_sys(pa.peer_flag[q], flagv);
+        if (fold) {
+            ok = wait_peer_flags(pa, flagv) ? 1 : 0;
+            if (ok) {
+                a = b = d = 0.0;
+                const double* sc = pa.scal_in + (j % kRing) * kMaxPeers * 4;
+                for (int q = 0; q < pa.nranks; ++q) {  // rank order: the same sum, bit for bit, on every rank
+                    a += ld_volatile_f64(sc + 4 * q + 0);
+                    b += ld_volatile_f64(sc + 4 * q + 1);
+                    d += ld_volatile_f64(sc + 4 * q + 2);
+                }
+            }
+        }
+    } else if (it.mode == MODE_SPLIT && fold) {
+        const double* sc = it.scal_glob + (j % kRing) * 4;
+        a = __ldcg(sc + 0);
+        b = __ldcg(sc + 1);
+        d = __ldcg(sc + 2);
     }
-    c.s = 1.0 / sqrt(c.qin);
+    if (!ok || *(volatile int*)&st->error) {
+        st->error = 1;
+        st->stop = STOP_ERROR;
+    } else if (fold) {
+        fold_launch(st, j, a, b, d);
+    } else if (have) {
+        st->folded = j + 1;  // launch j was a no-op
+    }
+    if (advance) {
+        LaunchCtrl nc;
+        nc.sigma = next_sigma(st, m);
+        nc.launch_no = m + 1;
+        nc.active = (st->stop == STOP_NONE && m + 1 <= st->max_trips) ? 1 : 0;
+        st->sigma[(m + 1) % kRing] = nc.sigma;
+        st->ctrl[(m + 1) % kRing] = nc;
+        st->launch_no = m + 1;
+    }
+}
+
+// Control-only launch (host poll / end): one CTA.
+template <class S>
+__global__ void __launch_bounds__(256) control_kernel(IterArgs<S> it) {
+    control_cta<S, 256>(it, false);
+}
+
+// -------------------------------------------------------------------------------------------------
+// Matvec CTAs: per-launch context, halo wait, peer sends, CTA finish.
+// -------------------------------------------------------------------------------------------------
+struct LaunchCtx {
+    int m, in, out, reverse;
+    double s;
+    unsigned long long flagv;  // peers' flag value that says the halo of v_m has landed
+};
+
+template <class S>
+__device__ __forceinline__ bool launch_begin(const IterArgs<S>& it, int phase, LaunchCtx& c) {
+    const LaunchCtrl ct = it.st->ctrl[phase];
+    if (!ct.active) return false;
+    c.m = ct.launch_no;
+    c.s = ct.sigma;
+    c.in = phase;
+    c.out = phase == kRing - 1 ? 0 : phase + 1;
+    c.reverse = it.serpentine & ct.launch_no & 1;
+    c.flagv = it.st->flag_base + (unsigned long long)ct.launch_no;
     return true;
 }
 
-template <class S, int BLOCK>
-__device__ __forceinline__ bool launch_prologue(const IterArgs<S>& it, LaunchCtx& c) {
-    __shared__ int s_wait_ok;
-    c.wait_ok = 1;
-    if (it.mode == MODE_PEER) {
-        if (threadIdx.x == 0) {
-            int ok = 1;
-            if (it.st->stop == STOP_NONE && it.st->pending && !(it.peer->debug & 4)) {
-                const PeerArgs& pa = *it.peer;
-                const unsigned long long want = (unsigned long long)(it.st->launches + 1);
-                const long long t0 = clock64();
-                for (int q = 0; q < pa.nranks && ok; ++q) {
-                    if (q == pa.rank) continue;
-                    while (ld_acquire_sys(pa.flag_in + q) < want) {
-                        if (clock64() - t0 > pa.spin_limit) {
-                            ok = 0;
-                            break;
-                        }
-                    }
-                }
-            }
-            s_wait_ok = ok;
-        }
-        __syncthreads();
-        c.wait_ok = s_wait_ok;
-    }
-    PowerState ns;
-    return derive_state<S>(it, ns, c);
+template <class S> __device__ __forceinline__ S* ring_buf(const IterArgs<S>& it, int i) {
+    return i == 0 ? it.buf[0] : (i == 1 ? it.buf[1] : it.buf[2]);
 }
 
-// No-op launch: if the prologue changed the state, the last CTA to get here writes it back.
+// Waits (thread 0 spins, the CTA follows) until the halo of v_m has landed; false on timeout.
 template <class S>
-__device__ __forceinline__ void finish_inactive(const IterArgs<S>& it, LaunchCtx& c) {
-    if (!c.dirty || threadIdx.x != 0) return;
-    const unsigned t = atomicAdd(&it.st->ticket, 1u);
-    if (t == gridDim.x - 1) {
-        PowerState ns;
-        derive_state<S>(it, ns, c);
-        ns.ticket = 0;
-        *it.st = ns;
-    }
-}
-
-// Active launch: CTA sums -> partial slot; the last CTA adds the slots in fixed order and either runs
-// the convergence test (MODE_FUSED) or publishes this rank's sums and its completion flag to every peer
-// (MODE_PEER).  slot / nslots: which partial slot this CTA owns and how many CTAs will report.
-template <class S, int BLOCK>
-__device__ __forceinline__ void grid_finish(const IterArgs<S>& it, LaunchCtx& c, double dre, double dim, double qn,
-                                            int slot, int nslots) {
-    __shared__ double sred[3][BLOCK / 32];
-    __shared__ int s_last;
-    cta_sum3<BLOCK>(dre, dim, qn, sred);
+__device__ __forceinline__ bool halo_wait(const IterArgs<S>& it, const LaunchCtx& c) {
+    __shared__ int s_ok;
     if (threadIdx.x == 0) {
-        it.partials[3 * slot + 0] = dre;
-        it.partials[3 * slot + 1] = dim;
-        it.partials[3 * slot + 2] = qn;
-    }
-    if (it.mode == MODE_SPLIT) return;
-    if (threadIdx.x == 0) {
-        if (it.mode == MODE_PEER && !(it.peer->debug & 1)) __threadfence_system();  // this CTA's remote halo stores
-        else __threadfence();
-        const unsigned t = atomicAdd(&it.st->ticket, 1u);
-        s_last = (t == unsigned(nslots - 1));
+        s_ok = wait_peer_flags(*it.peer, c.flagv) ? 1 : 0;
+        if (!s_ok) *(volatile int*)&it.st->error = 1;
     }
     __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    double a = 0.0, b = 0.0, d = 0.0;
-    for (int i = threadIdx.x; i < nslots; i += BLOCK) {
-        a += __ldcg(it.partials + 3 * i + 0);
-        b += __ldcg(it.partials + 3 * i + 1);
-        d += __ldcg(it.partials + 3 * i + 2);
-    }
-    cta_sum3<BLOCK>(a, b, d, sred);
-    if (it.mode == MODE_FUSED) {
-        if (threadIdx.x == 0) {
-            PowerState ns;
-            derive_state<S>(it, ns, c);
-            finalize_launch(&ns, a, b, d, c.l, c.in, c.qin);
-            ns.ticket = 0;
-            *it.st = ns;
-        }
-        return;
-    }
-    // MODE_PEER
-    const PeerArgs& pa = *it.peer;
-    const int par = c.l & 1;
-    // scattered send lists: rows other CTAs wrote, copied to the peers' halo segments
-    const S* outv = par ? it.buf0 : it.buf1;
-    for (int k = 0; k < pa.nlist; ++k) {
-        S* dst = static_cast<S*>(pa.list_dst[k][par ^ 1]);
-        const int32_t* idx = pa.send_idx + pa.list_off[k];
-        for (int i = threadIdx.x; i < pa.list_count[k]; i += BLOCK) dst[i] = Sc<S>::ldcg(outv + idx[i]);
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double* mine = pa.scal_in + par * kMaxPeers * 4 + pa.rank * 4;
-        mine[0] = a;
-        mine[1] = b;
-        mine[2] = d;
-        for (int q = 0; q < pa.nranks && !(pa.debug & 8); ++q) {
-            if (q == pa.rank) continue;
-            double* dst = pa.peer_scal[q] + par * kMaxPeers * 4 + pa.rank * 4;
-            dst[0] = a;
-            dst[1] = b;
-            dst[2] = d;
-        }
-        PowerState ns;
-        derive_state<S>(it, ns, c);
-        ns.pending = 1;
-        ns.ticket = 0;
-        *it.st = ns;
-        __threadfence_system();
-        for (int q = 0; q < pa.nranks && !(pa.debug & 8); ++q)
-            if (q != pa.rank) st_release_sys(pa.peer_flag[q], (unsigned long long)(c.l + 1));
-    }
+    return s_ok != 0;
 }
 
-// Row epilogue shared by every matvec kernel: z is (A u)_row * s already.  In MODE_PEER a row that a
-// peer's rows reference is also stored into that peer's halo segment (fire-and-forget NVLink store).
+// Contiguous send ranges of this launch, staged in shared memory once per CTA.
+struct SendSm {
+    int n;
+    int start[kMaxPeers];
+    int count[kMaxPeers];
+    void* dst[kMaxPeers];
+};
+
 template <class S>
-__device__ __forceinline__ void row_epilogue(const IterArgs<S>& it, const LaunchCtx& c, S z, S u_own, S* out, int row,
-                                             double& dre, double& dim, double& qn) {
-    const S x = Sc<S>::scale(u_own, c.s);
-    Sc<S>::dotc(x, z, dre, dim);
+__device__ __forceinline__ void load_sends(const IterArgs<S>& it, const LaunchCtx& c, SendSm& sm) {
+    if (threadIdx.x == 0) sm.n = it.mode == MODE_PEER ? it.peer->nsend : 0;
+    if (it.mode == MODE_PEER && threadIdx.x < kMaxPeers) {
+        sm.start[threadIdx.x] = it.peer->send_start[threadIdx.x];
+        sm.count[threadIdx.x] = it.peer->send_count[threadIdx.x];
+        sm.dst[threadIdx.x] = it.peer->send_dst[threadIdx.x][c.out];
+    }
+    __syncthreads();
+}
+
+// Row epilogue shared by every matvec kernel: z = sigma * (A v)_row.  A row that a peer's rows reference
+// is also stored into that peer's halo segment (fire-and-forget NVLink store).
+template <class S>
+__device__ __forceinline__ void row_epilogue(const SendSm& sm, S z, S v_own, S* out, int row, double& are, double& aim,
+                                             double& qn) {
+    Sc<S>::dotc(v_own, z, are, aim);
     qn += Sc<S>::abs2(z);
     out[row] = z;
-    if (it.mode == MODE_PEER) {
-        const PeerArgs& pa = *it.peer;
-        for (int k = 0; k < pa.nsend && !(pa.debug & 2); ++k) {
-            const unsigned off = unsigned(row - pa.send_start[k]);
-            if (off < unsigned(pa.send_count[k])) static_cast<S*>(pa.send_dst[k][(c.in ^ 1)])[off] = z;
+    for (int k = 0; k < sm.n; ++k) {
+        const unsigned off = unsigned(row - sm.start[k]);
+        if (off < unsigned(sm.count[k])) static_cast<S*>(sm.dst[k])[off] = z;
+    }
+}
+
+// CTA sums -> this CTA's partial slot of the launch (read by the next launch's control CTA).
+template <class S, int BLOCK>
+__device__ __forceinline__ void cta_finish(const IterArgs<S>& it, const LaunchCtx& c, double are, double aim, double qn,
+                                           int slot) {
+    __shared__ double sred[3][BLOCK / 32];
+    cta_sum3<BLOCK>(are, aim, qn, sred);
+    if (threadIdx.x == 0) {
+        double* part = it.partials + (size_t(c.in) * size_t(it.nslots) + size_t(slot)) * 3;
+        part[0] = are;
+        part[1] = aim;
+        part[2] = qn;
+    }
+}
+
+// Work-unit walk shared by the sparse kernels: pass 0 = units that read no halo entry, then (MODE_PEER)
+// the halo wait, then pass 1 = the deferred units.  Without a deferred map a multi-GPU peer launch
+// waits first.  `body(unit)` is called CTA-uniformly.
+template <class S, class F>
+__device__ __forceinline__ void walk_units(const IterArgs<S>& it, const LaunchCtx& c, int first, int stride, int nunits,
+                                           F&& body) {
+    const uint8_t* def = it.deferred;
+    if (it.mode == MODE_PEER && !def) {
+        if (!halo_wait<S>(it, c)) return;
+    }
+    for (int pass = 0; pass < (def ? 2 : 1); ++pass) {
+        if (pass == 1 && !halo_wait<S>(it, c)) return;
+        for (int i = first; i < nunits; i += stride) {
+            const int unit = c.reverse ? nunits - 1 - i : i;
+            if (def && def[unit] != pass) continue;
+            body(unit);
         }
     }
 }
@@ -487,46 +550,57 @@ __device__ __forceinline__ void row_epilogue(const IterArgs<S>& it, const Launch
 // =================================================================================================
 // CSR, one thread per row.  Right for very short rows; loads of vals/colidx are strided across the
 // warp but every fetched sector is consumed by the following loop trips out of L1.
+// Work unit = BLOCK consecutive rows.
 // =================================================================================================
 template <class S, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it) {
-    LaunchCtx c;
-    if (!launch_prologue<S, BLOCK>(it, c)) {
-        finish_inactive<S>(it, c);
+__global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
         return;
     }
-    const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
-    S* __restrict__ out = c.in ? it.buf0 : it.buf1;
-    double dre = 0.0, dim = 0.0, qn = 0.0;
-    for (int row = blockIdx.x * BLOCK + threadIdx.x; row < A.rows; row += gridDim.x * BLOCK) {
-        const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
-        S acc = Sc<S>::zero();
-        for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), Sc<S>::ldg(u + __ldg(A.colidx + p)));
-        row_epilogue<S>(it, c, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, dre, dim, qn);
-    }
-    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
+    __shared__ SendSm sends;
+    LaunchCtx c;
+    if (!launch_begin<S>(it, phase, c)) return;
+    load_sends<S>(it, c, sends);
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    double are = 0.0, aim = 0.0, qn = 0.0;
+    const int nunits = (A.rows + BLOCK - 1) / BLOCK;
+    walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nunits, [&](int unit) {
+        const int row = unit * BLOCK + threadIdx.x;
+        if (row < A.rows) {
+            const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
+            S acc = Sc<S>::zero();
+            for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), Sc<S>::ldg(u + __ldg(A.colidx + p)));
+            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, are, aim, qn);
+        }
+    });
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
 }
 
 // =================================================================================================
 // CSR, LANES lanes per row (LANES = 32 is warp-per-row).  Lanes stride over the row so each warp
 // instruction reads LANES consecutive values / indices; partial sums meet in a shuffle tree.
+// Work unit = BLOCK / LANES consecutive rows (one CTA-wide step).
 // =================================================================================================
 template <class S, int LANES, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, IterArgs<S> it) {
-    LaunchCtx c;
-    if (!launch_prologue<S, BLOCK>(it, c)) {
-        finish_inactive<S>(it, c);
+__global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
         return;
     }
-    const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
-    S* __restrict__ out = c.in ? it.buf0 : it.buf1;
-    double dre = 0.0, dim = 0.0, qn = 0.0;
+    __shared__ SendSm sends;
+    LaunchCtx c;
+    if (!launch_begin<S>(it, phase, c)) return;
+    load_sends<S>(it, c, sends);
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    double are = 0.0, aim = 0.0, qn = 0.0;
+    constexpr int RPU = BLOCK / LANES;  // rows per unit
     const int sub = threadIdx.x % LANES;
-    const int group = (blockIdx.x * BLOCK + threadIdx.x) / LANES;
-    const int ngroups = gridDim.x * (BLOCK / LANES);
-    // all lanes of a warp run the same number of trips so the full-mask shuffles stay converged
-    const int rows_rounded = (A.rows + (32 / LANES) - 1) / (32 / LANES) * (32 / LANES);
-    for (int row = group; row < rows_rounded; row += ngroups) {
+    const int nunits = (A.rows + RPU - 1) / RPU;
+    walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nunits, [&](int unit) {
+        const int row = unit * RPU + threadIdx.x / LANES;
         S acc = Sc<S>::zero();
         if (row < A.rows) {
             const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
@@ -536,9 +610,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
 #pragma unroll
         for (int d = LANES / 2; d > 0; d >>= 1) Sc<S>::add(acc, Sc<S>::shfl_down(acc, d, LANES));
         if (sub == 0 && row < A.rows)
-            row_epilogue<S>(it, c, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, dre, dim, qn);
-    }
-    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
+            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, are, aim, qn);
+    });
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
 }
 
 // =================================================================================================
@@ -547,6 +621,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
 // (16-byte value loads, 8-byte index loads, fully coalesced), multiplied with the gathered x and
 // parked in shared memory; then one thread per row sums its segment in ascending column order.
 // A row longer than the tile is its own block and is reduced by the whole CTA.
+// Work unit = one row block.
 // =================================================================================================
 template <class S> struct StreamCfg;
 template <> struct StreamCfg<double> { static constexpr int TILE = 4096; };   // 32 KB of products
@@ -555,21 +630,24 @@ constexpr int kStreamMaxRows = 512;
 
 template <class S, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, const int32_t* __restrict__ rowblk,
-                                                                int nblk, IterArgs<S> it) {
+                                                                int nblk, IterArgs<S> it, int phase) {
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
+        return;
+    }
     constexpr int TILE = StreamCfg<S>::TILE;
     __shared__ __align__(16) S prod[TILE];
     __shared__ int32_t srow[kStreamMaxRows + 1];
     __shared__ double slong[3][BLOCK / 32];
+    __shared__ SendSm sends;
     LaunchCtx c;
-    if (!launch_prologue<S, BLOCK>(it, c)) {
-        finish_inactive<S>(it, c);
-        return;
-    }
-    const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
-    S* __restrict__ out = c.in ? it.buf0 : it.buf1;
-    double dre = 0.0, dim = 0.0, qn = 0.0;
+    if (!launch_begin<S>(it, phase, c)) return;
+    load_sends<S>(it, c, sends);
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    double are = 0.0, aim = 0.0, qn = 0.0;
     const double* vals_d = reinterpret_cast<const double*>(A.vals);
-    for (int b = blockIdx.x; b < nblk; b += gridDim.x) {
+    walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nblk, [&](int b) {
         const int r0 = __ldg(rowblk + b), r1 = __ldg(rowblk + b + 1);
         const int nr = r1 - r0;
         for (int i = threadIdx.x; i <= nr; i += BLOCK) srow[i] = __ldg(A.rowptr + r0 + i);
@@ -593,7 +671,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                 S z;
                 if constexpr (Sc<S>::is_complex) z = make_double2(ar * c.s, ai * c.s);
                 else z = ar * c.s;
-                row_epilogue<S>(it, c, z, Sc<S>::ldg(u + r0), out, r0, dre, dim, qn);
+                row_epilogue<S>(sends, z, Sc<S>::ldg(u + r0), out, r0, are, aim, qn);
             }
         } else {
             for (int e = base + 2 * threadIdx.x; e < p1; e += 2 * BLOCK) {
@@ -615,12 +693,12 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                 S acc = Sc<S>::zero();
                 const int q1 = srow[i + 1] - base;
                 for (int q = srow[i] - base; q < q1; ++q) Sc<S>::add(acc, prod[q]);
-                row_epilogue<S>(it, c, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + r0 + i), out, r0 + i, dre, dim, qn);
+                row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + r0 + i), out, r0 + i, are, aim, qn);
             }
         }
         __syncthreads();
-    }
-    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
+    });
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
 }
 
 // =================================================================================================
@@ -628,22 +706,25 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
 // Entry j of those rows is stored at  slice_off + (j*32 + l)*R : one warp instruction reads 32*R
 // consecutive values (R=2, f64: 16-byte loads; c128: 16 bytes per value) and 32*R consecutive column
 // indices, and for stencil-like rows the x gathers of neighbouring lanes fall into the same lines.
-// No shared memory, no block barrier in the main loop.
+// No shared memory, no block barrier in the main loop.  Work unit = one slice (per warp).
 // =================================================================================================
 template <class S, int R, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArgs<S> it) {
-    LaunchCtx c;
-    if (!launch_prologue<S, BLOCK>(it, c)) {
-        finish_inactive<S>(it, c);
+__global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArgs<S> it, int phase) {
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
         return;
     }
-    const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
-    S* __restrict__ out = c.in ? it.buf0 : it.buf1;
-    double dre = 0.0, dim = 0.0, qn = 0.0;
+    __shared__ SendSm sends;
+    LaunchCtx c;
+    if (!launch_begin<S>(it, phase, c)) return;
+    load_sends<S>(it, c, sends);
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    double are = 0.0, aim = 0.0, qn = 0.0;
     const int lane = threadIdx.x & 31;
-    const int gwarp = (blockIdx.x * BLOCK + threadIdx.x) >> 5;
-    const int nwarps = gridDim.x * (BLOCK / 32);
-    for (int sl = gwarp; sl < A.nslices; sl += nwarps) {
+    const int gwarp = ((blockIdx.x - 1) * BLOCK + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x - 1) * (BLOCK / 32);
+    walk_units<S>(it, c, gwarp, nwarps, A.nslices, [&](int sl) {
         const int64_t off = __ldg(A.slice_off + sl);
         const int width = int((__ldg(A.slice_off + sl + 1) - off) / (32 * R));
         const S* vp = A.vals + off + lane * R;
@@ -681,33 +762,38 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 #pragma unroll
         for (int r = 0; r < R; ++r)
             if (row + r < A.rows)
-                row_epilogue<S>(it, c, Sc<S>::scale(acc[r], c.s), Sc<S>::ldg(u + row + r), out, row + r, dre, dim, qn);
-    }
-    grid_finish<S, BLOCK>(it, c, dre, dim, qn, blockIdx.x, gridDim.x);
+                row_epilogue<S>(sends, Sc<S>::scale(acc[r], c.s), Sc<S>::ldg(u + row + r), out, row + r, are, aim, qn);
+    });
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
 }
 
 // =================================================================================================
 // Dense column-major GEMV.  CTA (tile, seg) owns RT = BLOCK*R rows (R = 2 for f64 -> 16-byte loads
-// down a column, 1 for c128) and the columns of segment seg.  x = u*s of the segment is staged in
-// shared memory once per CTA.  Segment sums go to partial[seg][row]; the last CTA of a row tile adds
-// them in segment order (deterministic), runs the row epilogue and reports the tile's sums.
+// down a column, 1 for c128) and the columns of segment seg.  v of the segment is staged in shared
+// memory once per CTA.  Segment sums go to partial[seg][row]; the last CTA of a row tile adds them in
+// segment order (deterministic), runs the row epilogue and leaves the tile's sums in the tile's slot.
 // =================================================================================================
 constexpr int kGemvChunk = 512;  // columns of x staged per pass
 
 template <class S, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, IterArgs<S> it) {
+__global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, IterArgs<S> it, int phase) {
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
+        return;
+    }
     constexpr int R = Sc<S>::is_complex ? 1 : 2;
     constexpr int RT = BLOCK * R;
     __shared__ __align__(16) S xs[kGemvChunk];
     __shared__ int s_tile_last;
+    __shared__ SendSm sends;
     LaunchCtx c;
-    if (!launch_prologue<S, BLOCK>(it, c)) {
-        finish_inactive<S>(it, c);
-        return;
-    }
-    const S* __restrict__ u = c.in ? it.buf1 : it.buf0;
-    S* __restrict__ out = c.in ? it.buf0 : it.buf1;
-    const int tile = blockIdx.x / A.nseg, seg = blockIdx.x % A.nseg;
+    if (!launch_begin<S>(it, phase, c)) return;
+    load_sends<S>(it, c, sends);
+    if (it.mode == MODE_PEER && !halo_wait<S>(it, c)) return;  // every row reads the whole halo
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int cta = blockIdx.x - 1;
+    const int tile = cta / A.nseg, seg = cta % A.nseg;
     const int c0 = int(int64_t(A.cols) * seg / A.nseg), c1 = int(int64_t(A.cols) * (seg + 1) / A.nseg);
     const int r = tile * RT + threadIdx.x * R;
     const bool live = r < A.lda;  // lda is even and rows beyond A.rows are zero-filled on the device
@@ -748,36 +834,33 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     __syncthreads();
     if (!s_tile_last) return;
     __threadfence();
-    double dre = 0.0, dim = 0.0, qn = 0.0;
+    double are = 0.0, aim = 0.0, qn = 0.0;
 #pragma unroll
     for (int k = 0; k < R; ++k) {
         const int row = r + k;
         if (row < A.rows) {
             S z = Sc<S>::zero();
             for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
-            row_epilogue<S>(it, c, z, Sc<S>::ldg(u + row), out, row, dre, dim, qn);
+            row_epilogue<S>(sends, z, Sc<S>::ldg(u + row), out, row, are, aim, qn);
         }
     }
-    grid_finish<S, BLOCK>(it, c, dre, dim, qn, tile, A.ntiles);
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, tile);
 }
 
 // =================================================================================================
 // Small helper kernels.
 // =================================================================================================
-// Multi-GPU: fixed-order sum of the CTA partials into scal[3] (then NCCL all-reduces scal).
+// MODE_SPLIT: fixed-order sum of the CTA partials of launch j (ring slot) into scal[0..2]; NCCL
+// all-reduces scal in place and the next launch's control CTA folds it.
 template <int BLOCK>
-__global__ void __launch_bounds__(BLOCK) reduce_partials_kernel(const double* partials, int nslots, PowerState* st,
-                                                                double* scal) {
+__global__ void __launch_bounds__(BLOCK) reduce_partials_kernel(const double* partials, int nslots, double* scal) {
     __shared__ double sred[3][BLOCK / 32];
     double a = 0.0, b = 0.0, d = 0.0;
-    const int stop = st->stop;
-    const bool active = stop == STOP_NONE && st->launches <= st->max_trips && st->q[st->launches & 1] != 0.0;
-    if (active)
-        for (int i = threadIdx.x; i < nslots; i += BLOCK) {
-            a += partials[3 * i + 0];
-            b += partials[3 * i + 1];
-            d += partials[3 * i + 2];
-        }
+    for (int i = threadIdx.x; i < nslots; i += BLOCK) {
+        a += partials[3 * i + 0];
+        b += partials[3 * i + 1];
+        d += partials[3 * i + 2];
+    }
     cta_sum3<BLOCK>(a, b, d, sred);
     if (threadIdx.x == 0) {
         scal[0] = a;
@@ -786,39 +869,11 @@ __global__ void __launch_bounds__(BLOCK) reduce_partials_kernel(const double* pa
     }
 }
 
-// Multi-GPU: the state transition after the all-reduce; identical inputs on every rank, so every
-// rank takes the same decision without a broadcast.
-__global__ void finalize_kernel(PowerState* st, const double* scal) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    const int l = st->launches;
-    if (st->stop != STOP_NONE || l > st->max_trips) return;
-    const int in = l & 1;
-    const double qin = st->q[in];
-    if (qin == 0.0) {
-        zero_norm_stop(st, l, in);
-        return;
-    }
-    finalize_launch(st, scal[0], scal[1], scal[2], l, in, qin);
-}
-
-// MODE_PEER: folds the sums of the last executed launch into the state (run before the host reads it,
-// so that it sees the same state a single-GPU run would have after that launch).
-template <class S>
-__global__ void peer_flush_kernel(IterArgs<S> it) {
-    LaunchCtx c;
-    launch_prologue<S, 32>(it, c);
-    if (c.dirty && threadIdx.x == 0) {
-        PowerState ns;
-        derive_state<S>(it, ns, c);
-        ns.ticket = 0;
-        *it.st = ns;
-    }
-}
-
 // x = y / normY (power_method.hpp:78, true division) of the result buffer -> contiguous output.
 template <class S>
-__global__ void normalize_result_kernel(const S* buf0, const S* buf1, const PowerState* st, S* x, int n) {
-    const S* src = st->final_buf ? buf1 : buf0;
+__global__ void normalize_result_kernel(const S* buf0, const S* buf1, const S* buf2, const PowerState* st, S* x, int n) {
+    const int fb = st->final_buf;
+    const S* src = fb == 0 ? buf0 : (fb == 1 ? buf1 : buf2);
     const double nrm = sqrt(st->final_q);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         x[i] = Sc<S>::div(src[i], nrm);

@@ -52,7 +52,7 @@ def main():
     expect = os.environ.get("EIGSOL_B200_EXPECT_EXCHANGE")
     if expect:  # 2 = peer memory (fused kernel), 1 = NCCL send/recv + all-reduce
         assert info["exchange"] == {"peer": 2, "nccl": 1}[expect], info
-        assert info["kernels_per_trip"] == (1 if expect == "peer" else 3)
+        assert info["kernels_per_trip"] == (1 if expect == "peer" else 2)
     y = dm.matvec(x0)
     yref = orc.spmv_csc((n, n), rp, ci, v, x0)
     if np.max(np.abs(y - yref)) > 1e-14 * np.max(np.abs(yref)):
