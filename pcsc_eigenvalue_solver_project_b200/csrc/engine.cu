@@ -134,6 +134,7 @@ struct MatrixImpl {
     int nblk = 0;
     DevBuf d_deferred;  // MODE_PEER: per work unit of the chosen kernel, 1 = reads halo entries
     bool have_deferred = false;
+    int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
     int serpentine = 0;
 
     // dense layout
@@ -183,6 +184,7 @@ struct MatrixImpl {
         a.scal_glob = d_scal.as<double>();
         a.deferred = (xmode == MODE_PEER && have_deferred) ? d_deferred.as<uint8_t>() : nullptr;
         a.serpentine = serpentine;
+        a.unit_start = (xmode == MODE_PEER && have_deferred) ? unit_start : 0;
         return a;
     }
     void alloc_vectors();
@@ -385,6 +387,7 @@ void MatrixImpl::setup_peer() {
         ipc_opened.clear();
         return;
     }
+    if (env_int("EIGSOL_B200_DEBUG_NOSEND", 0)) pa.nsend = pa.nlist = 0;  // timing experiments only: results are wrong
     peer_h = pa;
     d_peer.alloc(sizeof(PeerArgs));
     EIGSOL_CUDA(cudaMemcpy(d_peer.p, &pa, sizeof pa, cudaMemcpyHostToDevice));
@@ -610,7 +613,9 @@ void MatrixImpl::configure_launch() {
 // processed after the halo wait, everything else before it (kernels.cuh: walk_units).
 void MatrixImpl::build_deferred() {
     have_deferred = false;
+    unit_start = 0;
     if (dense || xmode != MODE_PEER || nhalo == 0 || csr.rowptr.empty()) return;
+    if (!env_int("EIGSOL_B200_DEFER", 1)) return;  // 0: every CTA waits for the halo before its first row
     int64_t nunits = 0;
     auto unit_of_row = [&](int64_t r) -> int64_t { return r; };
     (void)unit_of_row;
@@ -639,6 +644,23 @@ void MatrixImpl::build_deferred() {
         r1 = std::min<int64_t>(r1, nloc);
         for (int64_t r = r0; r < r1 && !def[size_t(u)]; ++r)
             if (row_reads_halo(r)) def[size_t(u)] = 1;
+    }
+    // longest circular run of units that read no halo entry; the walk starts in its middle
+    {
+        int64_t best_len = 0, best_begin = 0, run = 0;
+        for (int64_t k = 0; k < 2 * nunits; ++k) {
+            const int64_t u = k % nunits;
+            if (def[size_t(u)]) {
+                run = 0;
+            } else {
+                ++run;
+                if (run > best_len && run <= nunits) {
+                    best_len = run;
+                    best_begin = k - run + 1;
+                }
+            }
+        }
+        unit_start = nunits > 0 ? int((best_begin + best_len / 2) % nunits) : 0;
     }
     d_deferred.alloc(def.size());
     d_deferred.upload(def.data(), def.size(), stream);

@@ -282,8 +282,9 @@ template <class S> struct IterArgs {
     int mode;                // MODE_*
     const PeerArgs* peer;    // device copy (MODE_PEER), else nullptr
     const double* scal_glob; // MODE_SPLIT: [kRing][4] all-reduced sums of launch j at slot j%3
-    const uint8_t* deferred; // MODE_PEER: per work unit, 1 = reads halo entries (done after the halo wait); may be null
+    const uint8_t* deferred; // MODE_PEER: per work unit, 1 = reads halo entries (needs the halo wait first); may be null
     int serpentine;          // odd launches walk the work units backwards (what was touched last is re-read first: L2)
+    int unit_start;          // rotation of the unit walk (see walk_units)
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
@@ -468,16 +469,22 @@ template <class S> __device__ __forceinline__ S* ring_buf(const IterArgs<S>& it,
     return i == 0 ? it.buf[0] : (i == 1 ? it.buf[1] : it.buf[2]);
 }
 
-// Waits (thread 0 spins, the CTA follows) until the halo of v_m has landed; false on timeout.
+// Waits until the halo of v_m has landed.  On a timeout the error flag is raised (the control CTA turns it
+// into STOP_ERROR) and the caller carries on.  Warp form: lane 0 spins, the warp follows (used mid-walk,
+// where the flags have normally arrived long ago).  CTA form: thread 0 spins, the CTA follows.
 template <class S>
-__device__ __forceinline__ bool halo_wait(const IterArgs<S>& it, const LaunchCtx& c) {
-    __shared__ int s_ok;
+__device__ __forceinline__ void halo_wait_warp(const IterArgs<S>& it, const LaunchCtx& c) {
+    if ((threadIdx.x & 31) == 0) {
+        if (!wait_peer_flags(*it.peer, c.flagv)) *(volatile int*)&it.st->error = 1;
+    }
+    __syncwarp();
+}
+template <class S>
+__device__ __forceinline__ void halo_wait_cta(const IterArgs<S>& it, const LaunchCtx& c) {
     if (threadIdx.x == 0) {
-        s_ok = wait_peer_flags(*it.peer, c.flagv) ? 1 : 0;
-        if (!s_ok) *(volatile int*)&it.st->error = 1;
+        if (!wait_peer_flags(*it.peer, c.flagv)) *(volatile int*)&it.st->error = 1;
     }
     __syncthreads();
-    return s_ok != 0;
 }
 
 // Contiguous send ranges of this launch, staged in shared memory once per CTA.
@@ -527,23 +534,28 @@ __device__ __forceinline__ void cta_finish(const IterArgs<S>& it, const LaunchCt
     }
 }
 
-// Work-unit walk shared by the sparse kernels: pass 0 = units that read no halo entry, then (MODE_PEER)
-// the halo wait, then pass 1 = the deferred units.  Without a deferred map a multi-GPU peer launch
-// waits first.  `body(unit)` is called CTA-uniformly.
+// Work-unit walk shared by the sparse kernels.  Units are visited in a rotated order that starts in the
+// middle of the longest run of units that read no halo entry (it.unit_start, planned on the host), so the
+// units that do read halo entries come up mid-kernel -- long after the peers' flags have arrived -- in
+// both walking directions; a warp waits for the flags (once) right before its first such unit.  Without a
+// deferred map a multi-GPU peer launch waits first.  Odd launches walk backwards (serpentine).
 template <class S, class F>
 __device__ __forceinline__ void walk_units(const IterArgs<S>& it, const LaunchCtx& c, int first, int stride, int nunits,
                                            F&& body) {
-    const uint8_t* def = it.deferred;
-    if (it.mode == MODE_PEER && !def) {
-        if (!halo_wait<S>(it, c)) return;
+    const uint8_t* def = it.mode == MODE_PEER ? it.deferred : nullptr;
+    bool waited = it.mode != MODE_PEER;
+    if (!waited && !def) {
+        halo_wait_cta<S>(it, c);
+        waited = true;
     }
-    for (int pass = 0; pass < (def ? 2 : 1); ++pass) {
-        if (pass == 1 && !halo_wait<S>(it, c)) return;
-        for (int i = first; i < nunits; i += stride) {
-            const int unit = c.reverse ? nunits - 1 - i : i;
-            if (def && def[unit] != pass) continue;
-            body(unit);
+    for (int i = first; i < nunits; i += stride) {
+        int unit = (c.reverse ? nunits - 1 - i : i) + it.unit_start;
+        if (unit >= nunits) unit -= nunits;
+        if (!waited && def[unit]) {
+            halo_wait_warp<S>(it, c);
+            waited = true;
         }
+        body(unit);
     }
 }
 
@@ -789,7 +801,7 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    if (it.mode == MODE_PEER && !halo_wait<S>(it, c)) return;  // every row reads the whole halo
+    if (it.mode == MODE_PEER) halo_wait_cta<S>(it, c);  // every row reads the whole halo
     const S* __restrict__ u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
     const int cta = blockIdx.x - 1;

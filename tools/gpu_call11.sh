@@ -1,0 +1,4 @@
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu11.log 2>&1; echo "rc=$?"; tail -5 gpurun_out/pytest_gpu11.log
+T="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/latency_bench.py 16 64 128 256"
+echo default; timeout 200 $T 2>/dev/null | grep '^{' | cut -c1-120
+echo nodefer; EIGSOL_B200_DEFER=0 timeout 200 $T 2>/dev/null | grep '^{' | cut -c1-120
