@@ -387,6 +387,10 @@ void MatrixImpl::setup_peer() {
         ipc_opened.clear();
         return;
     }
+    pa.debug_nowait = env_int("EIGSOL_B200_DEBUG_NOWAIT", 0);
+    pa.halo_src_mask = 0;
+    for (int q = 0; q < nranks; ++q)
+        if (q != rank && halo.peer_count[size_t(q)] > 0) pa.halo_src_mask |= 1u << q;
     if (env_int("EIGSOL_B200_DEBUG_NOSEND", 0)) pa.nsend = pa.nlist = 0;  // timing experiments only: results are wrong
     peer_h = pa;
     d_peer.alloc(sizeof(PeerArgs));

@@ -271,6 +271,8 @@ struct PeerArgs {
     double* scal_in;                  // local [kRing][kMaxPeers][4]
     unsigned long long* flag_in;      // local [kMaxPeers]
     long long spin_limit;             // clock64 ticks before a wait gives up (error -> STOP_ERROR)
+    int debug_nowait;                 // timing experiments only: waits return at once (results are wrong)
+    unsigned halo_src_mask;           // ranks that own halo entries of this rank (the ones a matvec warp waits for)
 };
 
 // Everything a matvec launch needs besides the matrix.
@@ -301,11 +303,22 @@ __device__ __forceinline__ double ld_volatile_f64(const double* p) {
     return v;
 }
 
-// Spins (one thread) until every peer's flag has reached `want`; false on timeout.
-__device__ __forceinline__ bool wait_peer_flags(const PeerArgs& pa, unsigned long long want) {
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Spins (one thread, acquire loads: measured cheaper than relaxed loads + a system fence) until the flags of
+// the peers in `mask` have reached `want`; false on timeout.
+__device__ __forceinline__ bool wait_peer_flags(const PeerArgs& pa, unsigned mask, unsigned long long want) {
+    if (pa.debug_nowait) return true;
     const long long t0 = clock64();
     for (int q = 0; q < pa.nranks; ++q) {
-        if (q == pa.rank) continue;
+        if (q == pa.rank || !((mask >> q) & 1u)) continue;
         while (ld_acquire_sys(pa.flag_in + q) < want)
             if (clock64() - t0 > pa.spin_limit) return false;
     }
@@ -379,37 +392,55 @@ __device__ void control_cta(const IterArgs<S>& it, bool advance) {
         }
         if (pa.nlist) __threadfence_system();
     }
+    __shared__ double s_tot[3];
+    __shared__ int s_okv[kMaxPeers];
+    if (threadIdx.x == 0) {
+        s_tot[0] = a;
+        s_tot[1] = b;
+        s_tot[2] = d;
+    }
     __syncthreads();
+    if (it.mode == MODE_PEER) {
+        // thread q talks to rank q, all peers in parallel: sums of launch j into q's mailbox, then (release) the
+        // flag "my launches < m are complete (your halo of v_m has landed) and my sums of launch m-1
+        // are with you"; then wait for q's flag in return.
+        const PeerArgs& pa = *it.peer;
+        const int q = threadIdx.x;
+        if (q < pa.nranks) {
+            int okq = 1;
+            const int slot = ((j + kRing) % kRing) * kMaxPeers * 4 + pa.rank * 4;
+            if (q == pa.rank) {
+                if (fold) {
+                    pa.scal_in[slot + 0] = s_tot[0];
+                    pa.scal_in[slot + 1] = s_tot[1];
+                    pa.scal_in[slot + 2] = s_tot[2];
+                }
+            } else {
+                if (fold) {
+                    double* dst = pa.peer_scal[q] + slot;
+                    dst[0] = s_tot[0];
+                    dst[1] = s_tot[1];
+                    dst[2] = s_tot[2];
+                }
+                st_release_sys(pa.peer_flag[q], flagv);
+                if (fold) okq = wait_peer_flags(pa, 1u << q, flagv) ? 1 : 0;
+            }
+            s_okv[q] = okq;
+        }
+        __syncthreads();
+    }
     if (threadIdx.x != 0) return;
     int ok = 1;
     if (it.mode == MODE_PEER) {
         const PeerArgs& pa = *it.peer;
-        if (fold) {
-            const int slot = (j % kRing) * kMaxPeers * 4 + pa.rank * 4;
-            pa.scal_in[slot + 0] = a;
-            pa.scal_in[slot + 1] = b;
-            pa.scal_in[slot + 2] = d;
-            for (int q = 0; q < pa.nranks; ++q) {
-                if (q == pa.rank) continue;
-                double* dst = pa.peer_scal[q] + slot;
-                dst[0] = a;
-                dst[1] = b;
-                dst[2] = d;
-            }
-        }
-        // "my launches < m are complete (your halo of v_m has landed) and my sums of launch m-1 are with you"
-        for (int q = 0; q < pa.nranks; ++q)
-            if (q != pa.rank) st_release_sys(pa.peer_flag[q], flagv);
-        if (fold) {
-            ok = wait_peer_flags(pa, flagv) ? 1 : 0;
-            if (ok) {
-                a = b = d = 0.0;
-                const double* sc = pa.scal_in + (j % kRing) * kMaxPeers * 4;
-                for (int q = 0; q < pa.nranks; ++q) {  // rank order: the same sum, bit for bit, on every rank
-                    a += ld_volatile_f64(sc + 4 * q + 0);
-                    b += ld_volatile_f64(sc + 4 * q + 1);
-                    d += ld_volatile_f64(sc + 4 * q + 2);
-                }
+        for (int q = 0; q < pa.nranks; ++q) ok &= s_okv[q];
+        if (fold && ok) {
+            a = b = d = 0.0;
+            const double* sc = pa.scal_in + (j % kRing) * kMaxPeers * 4;
+            for (int q = 0; q < pa.nranks; ++q) {  // rank order: the same sum, bit for bit, on every rank
+                a += ld_volatile_f64(sc + 4 * q + 0);
+                b += ld_volatile_f64(sc + 4 * q + 1);
+                d += ld_volatile_f64(sc + 4 * q + 2);
             }
         }
     } else if (it.mode == MODE_SPLIT && fold) {
@@ -475,14 +506,14 @@ template <class S> __device__ __forceinline__ S* ring_buf(const IterArgs<S>& it,
 template <class S>
 __device__ __forceinline__ void halo_wait_warp(const IterArgs<S>& it, const LaunchCtx& c) {
     if ((threadIdx.x & 31) == 0) {
-        if (!wait_peer_flags(*it.peer, c.flagv)) *(volatile int*)&it.st->error = 1;
+        if (!wait_peer_flags(*it.peer, it.peer->halo_src_mask, c.flagv)) *(volatile int*)&it.st->error = 1;
     }
     __syncwarp();
 }
 template <class S>
 __device__ __forceinline__ void halo_wait_cta(const IterArgs<S>& it, const LaunchCtx& c) {
     if (threadIdx.x == 0) {
-        if (!wait_peer_flags(*it.peer, c.flagv)) *(volatile int*)&it.st->error = 1;
+        if (!wait_peer_flags(*it.peer, it.peer->halo_src_mask, c.flagv)) *(volatile int*)&it.st->error = 1;
     }
     __syncthreads();
 }

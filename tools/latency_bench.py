@@ -27,28 +27,43 @@ def main():
         dist.broadcast(idt, 0)
         comm = es.Comm(rank, world, idt.cpu().numpy().tobytes(), local)
     grids = [int(a) for a in sys.argv[1:]] or [16, 64, 128, 256]
-    for g in grids:
-        n = g ** 3
-        lo, hi = n * rank // world, n * (rank + 1) // world
-        rp, ci, v = gen.laplacian_3d(g, lo, hi)
-        dm = es.DeviceMatrix.from_csr_rows(n, lo, rp, ci, v, comm)
-        x0 = es.random_unit(n, np.float64, seed=1)
-        dm.begin(x0, 2 ** 31 - 2, -1.0)
-        dm.step(64)
-        best = 1e30
-        for _ in range(3):
-            ms = dm.step(320)
-            if comm is not None:
-                ms = comm.max_float(ms)
-            best = min(best, ms)
-        info = dm.info()
-        r = dm.end(want_vector=False)
-        if rank == 0:
-            print(json.dumps({"g": g, "n": n, "world": world, "us_per_trip": best / 320 * 1e3, "exchange": info["exchange"],
-                              "kernel": info["kernel_name"], "debug": os.environ.get("EIGSOL_B200_PEER_DEBUG", "0"),
-                              "alg_GBps_per_rank": info["alg_bytes"] / (best / 320 * 1e-3) / 1e9,
-                              "lambda": repr(r.eigenvalue)}), flush=True)
-        dm.close()
+    # LAT_CONFIGS="name:K=V,K=V;name2:K=V" runs every grid under each set of library knobs (read at matrix creation)
+    configs = [("default", {})]
+    if os.environ.get("LAT_CONFIGS"):
+        configs = []
+        for item in os.environ["LAT_CONFIGS"].split(";"):
+            name, _, kv = item.partition(":")
+            configs.append((name, dict(p.split("=") for p in kv.split(",") if p)))
+    for cfg_name, cfg_env in configs:
+      for k in [k for k in os.environ if k.startswith("EIGSOL_B200_") and k not in ("EIGSOL_B200_EXCHANGE",)]:
+          del os.environ[k]
+      os.environ.update(cfg_env)
+      for g in grids:
+          n = g ** 3
+          lo, hi = n * rank // world, n * (rank + 1) // world
+          rp, ci, v = gen.laplacian_3d(g, lo, hi)
+          dm = es.DeviceMatrix.from_csr_rows(n, lo, rp, ci, v, comm)
+          x0 = es.random_unit(n, np.float64, seed=1)
+          dm.begin(x0, 2 ** 31 - 2, -1.0)
+          dm.step(64)
+          best = 1e30
+          for _ in range(3):
+              ms = dm.step(320)
+              mine = ms
+              if comm is not None:
+                  ms = comm.max_float(ms)
+              if ms < best:
+                  best, best_mine = ms, mine
+          info = dm.info()
+          r = dm.end(want_vector=False)
+          if world > 1 and os.environ.get("LAT_PER_RANK"):
+              print(f"# cfg={cfg_name} g={g} rank={rank} us={best_mine / 320 * 1e3:.2f}", flush=True)
+          if rank == 0:
+              print(json.dumps({"g": g, "n": n, "world": world, "us_per_trip": best / 320 * 1e3, "exchange": info["exchange"],
+                                "kernel": info["kernel_name"], "cfg": cfg_name,
+                                "alg_GBps_per_rank": info["alg_bytes"] / (best / 320 * 1e-3) / 1e9,
+                                "lambda": repr(r.eigenvalue)}), flush=True)
+          dm.close()
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
