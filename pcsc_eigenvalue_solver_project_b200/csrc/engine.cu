@@ -136,6 +136,7 @@ struct MatrixImpl {
     bool have_deferred = false;
     int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
     int serpentine = 0;
+    bool pdl = true;  // programmatic dependent launch of the matvec kernels
 
     // dense layout
     DevBuf d_dense, d_dense_partial, d_tile_ticket;
@@ -227,6 +228,7 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     d_state.alloc(sizeof(PowerState));
     d_scal.alloc(kRing * 4 * sizeof(double));
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
+    pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
     h_state.alloc(sizeof(PowerState));
 }
 
@@ -674,6 +676,22 @@ void MatrixImpl::build_deferred() {
 
 // One matvec launch on `stream`.  All launches of a handle are identical (the kernels pick the
 // ping-pong buffer from the device state), which is what lets a CUDA graph of them be replayed.
+// Kernel launch with the programmatic-stream-serialization attribute (PDL) when enabled.
+template <class... KArgs, class... Args>
+static void launch_pdl(bool pdl, cudaStream_t st, void (*kern)(KArgs...), dim3 g, dim3 b, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = g;
+    cfg.blockDim = b;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    EIGSOL_CUDA(cudaLaunchKernelEx(&cfg, kern, KArgs(args)...));
+}
+
 template <class S> static void launch_sparse(MatrixImpl& m, int ph) {
     constexpr int B = 256;
     IterArgs<S> it = m.iter_args<S>();
@@ -681,22 +699,22 @@ template <class S> static void launch_sparse(MatrixImpl& m, int ph) {
     const dim3 g(m.grid), b(B);
     cudaStream_t st = m.stream;
     switch (m.kernel) {
-        case K_CSR_SCALAR: spmv_csr_scalar_kernel<S, B><<<g, b, 0, st>>>(A, it, ph); break;
-        case K_CSR_STREAM: spmv_csr_stream_kernel<S, B><<<g, b, 0, st>>>(A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
+        case K_CSR_SCALAR: launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B>, g, b, A, it, ph); break;
+        case K_CSR_STREAM: launch_pdl(m.pdl, st, spmv_csr_stream_kernel<S, B>, g, b, A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
         case K_SELL: {
             SellView<S> V{int32_t(m.nloc), int32_t(m.sell_nslices), m.d_sell_off.as<int64_t>(), m.d_sell_col.as<int32_t>(),
                           m.d_sell_val.as<S>()};
-            if (m.lanes == 2) spmv_sell_kernel<S, 2, B><<<g, b, 0, st>>>(V, it, ph);
-            else spmv_sell_kernel<S, 1, B><<<g, b, 0, st>>>(V, it, ph);
+            if (m.lanes == 2) launch_pdl(m.pdl, st, spmv_sell_kernel<S, 2, B>, g, b, V, it, ph);
+            else launch_pdl(m.pdl, st, spmv_sell_kernel<S, 1, B>, g, b, V, it, ph);
             break;
         }
         case K_CSR_VECTOR:
             switch (m.lanes) {
-                case 2: spmv_csr_vector_kernel<S, 2, B><<<g, b, 0, st>>>(A, it, ph); break;
-                case 4: spmv_csr_vector_kernel<S, 4, B><<<g, b, 0, st>>>(A, it, ph); break;
-                case 8: spmv_csr_vector_kernel<S, 8, B><<<g, b, 0, st>>>(A, it, ph); break;
-                case 16: spmv_csr_vector_kernel<S, 16, B><<<g, b, 0, st>>>(A, it, ph); break;
-                default: spmv_csr_vector_kernel<S, 32, B><<<g, b, 0, st>>>(A, it, ph); break;
+                case 2: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 2, B>, g, b, A, it, ph); break;
+                case 4: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 4, B>, g, b, A, it, ph); break;
+                case 8: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 8, B>, g, b, A, it, ph); break;
+                case 16: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 16, B>, g, b, A, it, ph); break;
+                default: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 32, B>, g, b, A, it, ph); break;
             }
             break;
         default: throw StateError("no sparse kernel selected");
@@ -708,7 +726,7 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
-    gemv_colmajor_kernel<S, B><<<dim3(m.grid), dim3(B), 0, m.stream>>>(A, it, ph);
+    launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B>, dim3(m.grid), dim3(B), A, it, ph);
 }
 
 void MatrixImpl::launch_matvec(int phase) {

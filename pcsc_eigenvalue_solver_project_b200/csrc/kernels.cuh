@@ -357,6 +357,14 @@ __device__ __forceinline__ void cta_sum3(double& a, double& b, double& c, double
     __syncthreads();
 }
 
+// Programmatic dependent launch: every matvec kernel lets its successor's CTAs become resident at once
+// (they fill the SM slots this launch's tail frees) and itself waits here for its predecessor to have
+// completed and flushed before it reads anything that launch wrote.  No-ops without the launch attribute.
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // -------------------------------------------------------------------------------------------------
 // The control CTA: blockIdx.x == 0 of every matvec launch (advance = true), and the whole of
 // control_kernel (advance = false: folds what is pending so the host reads a settled state).
@@ -597,6 +605,7 @@ __device__ __forceinline__ void walk_units(const IterArgs<S>& it, const LaunchCt
 // =================================================================================================
 template <class S, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
@@ -628,6 +637,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
 // =================================================================================================
 template <class S, int LANES, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
@@ -674,6 +684,7 @@ constexpr int kStreamMaxRows = 512;
 template <class S, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, const int32_t* __restrict__ rowblk,
                                                                 int nblk, IterArgs<S> it, int phase) {
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
@@ -753,6 +764,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
 // =================================================================================================
 template <class S, int R, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArgs<S> it, int phase) {
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
@@ -820,6 +832,7 @@ constexpr int kGemvChunk = 512;  // columns of x staged per pass
 
 template <class S, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, IterArgs<S> it, int phase) {
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
