@@ -5,6 +5,8 @@
 // issues launches and polls the device-resident PowerState; no arithmetic of the path runs on the CPU
 // and there is no CPU fallback: without a CUDA device every compute entry point fails loudly.
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -14,6 +16,7 @@
 #include <vector>
 
 #include "../../include/eigsol_b200.h"
+#include "ingest.cuh"
 #include "kernels.cuh"
 #include "plan.hpp"
 #include "runtime.hpp"
@@ -33,6 +36,20 @@ struct Comm {
     ~Comm() {
         if (nccl_comm) nccl().CommDestroy(nccl_comm);
         if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+// EIGSOL_B200_TRACE=1: wall-clock phase marks on stderr (setup paths only)
+struct Trace {
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    Trace() : on(std::getenv("EIGSOL_B200_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    void mark(const char* what) {
+        if (!on) return;
+        cudaDeviceSynchronize();
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[eigsol_b200] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
     }
 };
 
@@ -171,6 +188,8 @@ struct MatrixImpl {
 
     void init_common(int dtype_, Comm* comm_);
     void init_sparse_local(CsrHost&& local_global_cols);
+    void init_sparse_device_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner, const void* values);
+    void ensure_host_csr();
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
     void plan_exchange();
     void setup_peer();
@@ -442,6 +461,131 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     else set_kernel(ch.kernel, ch.lanes);
 }
 
+// -------------------------------------------------------------------------------------------------
+// Single GPU, CSC input: staged multi-threaded upload + transpose on the device (ingest.cuh).
+// The host keeps no CSR copy; ensure_host_csr() fetches one if a derived layout has to be built.
+// -------------------------------------------------------------------------------------------------
+void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                                        const void* values) {
+    dense = false;
+    if (rows > INT32_MAX || cols > INT32_MAX) throw PlanError("matrix dimension exceeds int32 indices");
+    if (!outer) throw PlanError("null outer index array");
+    if (outer[0] != 0) throw PlanError("CSC outer index must start at 0 (compressed storage expected)");
+    for (int64_t j = 0; j < cols; ++j)
+        if (outer[j + 1] < outer[j]) throw PlanError("CSC outer index not monotone");
+    const int64_t nnz = outer[cols];
+    if (nnz > 0 && (!inner || !values)) throw PlanError("null inner index array");
+    row_begin.assign({0, rows});
+    lo = 0;
+    hi = nloc = rows;
+    local_nnz = nnz_global = nnz;
+    halo = HaloPlan();
+    halo.peer_count.assign(1, 0);
+    halo.peer_off.assign(2, 0);
+    nhalo = 0;
+    alloc_vectors();
+    if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
+    plan_exchange();
+    setup_peer();
+    csr = CsrHost();
+    csr.dtype = dtype;
+    csr.rows = rows;
+    csr.cols = ext_len;
+    Trace tr;
+    tr.mark("ingest: validate+vectors");
+    const size_t s = size_t(ss());
+    const size_t nz = size_t(std::max<int64_t>(nnz, 1));
+    d_rowptr.alloc(sizeof(int32_t) * size_t(rows + 1));  // zero-filled: the row histogram
+    d_colidx.alloc(sizeof(int32_t) * nz);
+    d_vals.alloc(nz * s);
+    stats = RowStats();
+    stats.rows = rows;
+    stats.nnz = nnz;
+    if (nnz > 0) {
+        DevBuf d_outer, d_inner, d_cvals, d_col, d_iota, d_perm, d_keys, d_flags, d_tmp, d_tmp2;
+        d_outer.alloc(sizeof(int32_t) * size_t(cols + 1));
+        d_inner.alloc(sizeof(int32_t) * nz);
+        d_cvals.alloc(nz * s);
+        d_col.alloc(sizeof(int32_t) * nz);
+        d_iota.alloc(sizeof(int32_t) * nz);
+        d_perm.alloc(sizeof(int32_t) * nz);
+        d_keys.alloc(sizeof(int32_t) * nz);
+        d_flags.alloc(64);
+        tr.mark("ingest: device allocs");
+        StagedUploader up;
+        up.add(d_outer.p, outer, sizeof(int32_t) * size_t(cols + 1));
+        up.add(d_inner.p, inner, sizeof(int32_t) * size_t(nnz));
+        up.add(d_cvals.p, values, size_t(nnz) * s);
+        EIGSOL_CUDA(up.run(device, env_int("EIGSOL_B200_UPLOAD_THREADS", 2)));
+        tr.mark("ingest: staged upload");
+        const int B = 256;
+        const unsigned gnz = unsigned((nnz + B - 1) / B);
+        csc_expand_kernel<<<gnz, B, 0, stream>>>(d_outer.as<int32_t>(), d_inner.as<int32_t>(), cols, rows, nnz,
+                                                  d_col.as<int32_t>(), d_iota.as<int32_t>(), d_rowptr.as<int32_t>(),
+                                                  d_flags.as<int>());
+        int end_bit = 1;
+        while (end_bit < 31 && (int64_t(1) << end_bit) < rows) ++end_bit;
+        size_t tb = 0, tb2 = 0;
+        EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_inner.as<int32_t>(), d_keys.as<int32_t>(),
+                                                    d_iota.as<int32_t>(), d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
+        d_tmp.alloc(tb);
+        EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(d_tmp.p, tb, d_inner.as<int32_t>(), d_keys.as<int32_t>(),
+                                                    d_iota.as<int32_t>(), d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(rows + 1), stream));
+        d_tmp2.alloc(tb2);
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp2.p, tb2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(rows + 1), stream));
+        if (dtype)
+            csc_gather_kernel<double2><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_cvals.as<double2>(), nnz,
+                                                              d_colidx.as<int32_t>(), d_vals.as<double2>());
+        else
+            csc_gather_kernel<double><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_cvals.as<double>(), nnz,
+                                                             d_colidx.as<int32_t>(), d_vals.as<double>());
+        // row-length statistics for the kernel choice
+        int* f = d_flags.as<int>();  // [0] error flags, [1] max, [2] min, [4..5] padded (u64), [6..7] var (double)
+        const int init_min = INT32_MAX;
+        EIGSOL_CUDA(cudaMemcpyAsync(f + 2, &init_min, sizeof(int), cudaMemcpyHostToDevice, stream));
+        stats.mean = double(nnz) / double(rows);
+        const unsigned gsl = unsigned(((rows + 63) / 64 + B - 1) / B);
+        row_stats_kernel<<<gsl, B, 0, stream>>>(d_rowptr.as<int32_t>(), rows, stats.mean, f + 1, f + 2,
+                                                reinterpret_cast<unsigned long long*>(f + 4), reinterpret_cast<double*>(f + 6));
+        launches += 4;
+        EIGSOL_CUDA(cudaGetLastError());
+        int hf[8];
+        EIGSOL_CUDA(cudaMemcpyAsync(hf, f, sizeof hf, cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        tr.mark("ingest: transpose+stats");
+        if (hf[0] & 2) throw PlanError("CSC inner index out of range");
+        if (hf[0] & 1) throw PlanError("CSC outer index not monotone");
+        unsigned long long padded;
+        double var;
+        std::memcpy(&padded, hf + 4, sizeof padded);
+        std::memcpy(&var, hf + 6, sizeof var);
+        stats.max = hf[1];
+        stats.min = hf[2];
+        stats.cv = stats.mean > 0 ? std::sqrt(var / double(rows)) / stats.mean : 0.0;
+        stats.sell_fill = double(padded) / double(nnz);
+    }
+    const int forced = env_int("EIGSOL_B200_KERNEL", 0);
+    if (forced > 0 && forced <= K_SELL) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
+    else set_kernel(K_AUTO, 0);
+}
+
+// Derived layouts (SELL, row blocks, deferred maps) are built on the host from the CSR; after a device-side
+// ingest the host has none yet.
+void MatrixImpl::ensure_host_csr() {
+    if (dense || !csr.rowptr.empty()) return;
+    EIGSOL_CUDA(cudaSetDevice(device));
+    csr.rowptr.resize(size_t(nloc) + 1);
+    csr.colidx.resize(size_t(local_nnz));
+    csr.vals.resize(size_t(local_nnz) * size_t(csr.spd()));
+    EIGSOL_CUDA(cudaMemcpyAsync(csr.rowptr.data(), d_rowptr.p, sizeof(int32_t) * size_t(nloc + 1), cudaMemcpyDeviceToHost, stream));
+    if (local_nnz) {
+        EIGSOL_CUDA(cudaMemcpyAsync(csr.colidx.data(), d_colidx.p, sizeof(int32_t) * size_t(local_nnz), cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaMemcpyAsync(csr.vals.data(), d_vals.p, size_t(local_nnz) * size_t(ss()), cudaMemcpyDeviceToHost, stream));
+    }
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+}
+
 void MatrixImpl::drop_graph() {
     if (graph) cudaGraphExecDestroy(graph);
     graph = nullptr;
@@ -469,7 +613,7 @@ void MatrixImpl::set_kernel(int kernel_, int lanes_) {
     } else if (kernel_ == K_SELL) {
         if (lanes_ == 0) lanes_ = dtype ? 1 : 2;
         if (lanes_ != 1 && lanes_ != 2) throw PlanError("SELL rows per lane must be 1 or 2");
-        if (csr.rowptr.empty()) throw StateError("host CSR copy was released; SELL layout cannot be rebuilt");
+        ensure_host_csr();
         if (sell_R != lanes_) {
             SellHost s = build_sell(csr, lanes_);
             sell_R = lanes_;
@@ -486,7 +630,7 @@ void MatrixImpl::set_kernel(int kernel_, int lanes_) {
     } else if (kernel_ == K_CSR_STREAM) {
         lanes_ = 0;
         if (nblk == 0 && nloc > 0) {
-            if (csr.rowptr.empty()) throw StateError("host CSR copy was released; row blocks cannot be rebuilt");
+            ensure_host_csr();
             const int tile = dtype ? StreamCfg<double2>::TILE : StreamCfg<double>::TILE;
             rowblk_h = build_row_blocks(nloc, csr.rowptr.data(), tile, kStreamMaxRows);
             const std::vector<int32_t>& rb = rowblk_h;
@@ -948,7 +1092,9 @@ void MatrixImpl::end(void* x_out, double lambda_out[2], int* iters, int* conv) {
 // is y = A x0 of trip 0; the sums of launch l >= 1 close trip l-1; the poll folds the last ones).  The
 // host polls the device state between batches; launches issued past the stopping point are no-ops.
 void MatrixImpl::run(const void* x0, int max_it, double tol, void* x_out, double lambda_out[2], int* iters, int* conv) {
+    Trace tr;
     begin(x0, max_it, tol);
+    tr.mark("run: begin (x0 upload)");
     if (max_it > 0) {
         int64_t remaining = int64_t(max_it) + 1;
         int batch = env_int("EIGSOL_B200_POLL", 64);
@@ -960,7 +1106,9 @@ void MatrixImpl::run(const void* x0, int max_it, double tol, void* x_out, double
             if (poll_state().stop != STOP_NONE) break;
         }
     }
+    tr.mark("run: iterate");
     end(x_out, lambda_out, iters, conv);
+    tr.mark("run: end (normalise+download)");
 }
 
 // y = A x alone: launch 0 of the loop with ||x|| taken as 1 leaves A x un-normalised in buffer 1.
@@ -1090,6 +1238,11 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
         MatrixImpl& m = h->impl;
         m.init_common(dtype, comm ? &comm->impl : nullptr);
         m.n = rows;
+        if (m.nranks == 1 && env_int("EIGSOL_B200_DEVICE_INGEST", 1)) {
+            m.init_sparse_device_csc(rows, cols, outer, inner, values);
+            *out = h.release();
+            return int(EIGSOL_B200_OK);
+        }
         CsrHost g = csc_to_csr(dtype, rows, cols, outer, inner, values);
         m.row_begin = partition_rows(rows, g.rowptr.data(), m.nranks);
         if (m.nranks == 1) {

@@ -1,0 +1,177 @@
+// ingest.cuh -- device-side ingest of the reference's sparse matrix (single GPU).
+//
+// EigSol::Matrix::Sparse<Scalar> is Eigen::SparseMatrix<Scalar, ColMajor, int> (reference:
+// src/matrix/matrix.hpp:43-44), i.e. CSC.  The matvec kernels want CSR with ascending columns inside a row
+// (the reference's accumulation order, eigen/Eigen/src/SparseCore/SparseDenseProduct.h:101-110).  The
+// transpose used to be a counting sort on one host core (1.1 s for the 117M entries of the 256^3 Laplacian,
+// 20x the 200 power iterations that follow).  Here the three CSC arrays are pushed to the device through
+// pinned staging buffers by a few host threads, and the transpose runs there:
+//     col[p]    = column of entry p                       (binary search in outer, one thread per entry)
+//     perm      = stable radix sort of p by row = inner[p] (cub::DeviceRadixSort -- library code, setup only)
+//     rowptr    = exclusive scan of the row histogram
+//     colidx[k] = col[perm[k]],  vals[k] = values[perm[k]]
+// Stable sort + CSC order (column-major, rows ascending inside a column) = columns ascending inside a row.
+// This is setup, not the hot path: it runs once per Matrix.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstring>
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <thread>
+#include <vector>
+
+#include "runtime.hpp"
+
+namespace eigsol_b200 {
+
+// ---- host -> device copy of a large pageable array through pinned staging, several threads ----------
+// Pinned staging buffers live for the life of the process (cudaHostAlloc costs milliseconds): slot t
+// belongs to uploader thread t.  Callers are serialised by the API mutex.
+struct PinnedPool {
+    static constexpr int kMaxThreads = 16;
+    void* buf[kMaxThreads][2] = {};
+    static PinnedPool& get() {
+        static PinnedPool p;
+        return p;
+    }
+    cudaError_t ensure(int t, size_t bytes) {
+        for (int b = 0; b < 2; ++b)
+            if (!buf[t][b]) {
+                const cudaError_t e = cudaHostAlloc(&buf[t][b], bytes, cudaHostAllocDefault);
+                if (e != cudaSuccess) return e;
+            }
+        return cudaSuccess;
+    }
+};
+
+struct StagedUploader {
+    static constexpr size_t kChunk = size_t(16) << 20;
+    struct Job {
+        char* dst;
+        const char* src;
+        size_t bytes;
+    };
+    std::vector<Job> jobs;
+    void add(void* dst, const void* src, size_t bytes) {
+        for (size_t off = 0; off < bytes; off += kChunk)
+            jobs.push_back(Job{static_cast<char*>(dst) + off, static_cast<const char*>(src) + off,
+                               std::min(kChunk, bytes - off)});
+    }
+    // Runs all jobs; returns the first CUDA error seen (cudaSuccess if none).
+    cudaError_t run(int device, int nthreads) {
+        if (jobs.empty()) return cudaSuccess;
+        nthreads = int(std::max<size_t>(1, std::min<size_t>(size_t(nthreads), jobs.size())));
+        nthreads = std::min(nthreads, int(PinnedPool::kMaxThreads));
+        std::atomic<size_t> next{0};
+        std::atomic<int> err{int(cudaSuccess)};
+        auto worker = [&](int tid) {
+            cudaSetDevice(device);
+            void* pin[2] = {nullptr, nullptr};
+            cudaStream_t st = nullptr;
+            cudaEvent_t ev[2] = {nullptr, nullptr};
+            cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = PinnedPool::get().ensure(tid, kChunk);
+            for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+                pin[b] = PinnedPool::get().buf[tid][b];
+                e = cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming);
+            }
+            int b = 0;
+            bool used[2] = {false, false};
+            while (e == cudaSuccess) {
+                const size_t i = next.fetch_add(1);
+                if (i >= jobs.size()) break;
+                if (used[b]) e = cudaEventSynchronize(ev[b]);  // the DMA out of this buffer has finished
+                if (e != cudaSuccess) break;
+                std::memcpy(pin[b], jobs[i].src, jobs[i].bytes);
+                e = cudaMemcpyAsync(jobs[i].dst, pin[b], jobs[i].bytes, cudaMemcpyHostToDevice, st);
+                if (e == cudaSuccess) e = cudaEventRecord(ev[b], st);
+                used[b] = true;
+                b ^= 1;
+            }
+            if (st) {
+                const cudaError_t e2 = cudaStreamSynchronize(st);
+                if (e == cudaSuccess) e = e2;
+            }
+            for (int k = 0; k < 2; ++k)
+                if (ev[k]) cudaEventDestroy(ev[k]);
+            if (st) cudaStreamDestroy(st);
+            if (e != cudaSuccess) err.store(int(e));
+        };
+        std::vector<std::thread> pool;
+        for (int t = 1; t < nthreads; ++t) pool.emplace_back(worker, t);
+        worker(0);
+        for (auto& t : pool) t.join();
+        jobs.clear();
+        return cudaError_t(err.load());
+    }
+};
+
+// ---- kernels ----------------------------------------------------------------------------------------
+// flags: bit 0 = outer not monotone / outer[0] != 0, bit 1 = row index out of range
+__global__ void csc_check_outer_kernel(const int32_t* __restrict__ outer, int64_t cols, int* flags) {
+    const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (j == 0 && outer[0] != 0) atomicOr(flags, 1);
+    if (j < cols && outer[j + 1] < outer[j]) atomicOr(flags, 1);
+}
+
+// One thread per entry: its column (upper_bound in outer), iota, range check and the row histogram.
+__global__ void csc_expand_kernel(const int32_t* __restrict__ outer, const int32_t* __restrict__ inner, int64_t cols,
+                                  int64_t rows, int64_t nnz, int32_t* __restrict__ col, int32_t* __restrict__ iota,
+                                  int32_t* __restrict__ rowcount, int* flags) {
+    const int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (p >= nnz) return;
+    int64_t lo = 0, hi = cols;  // largest j with outer[j] <= p
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(outer + mid) <= p) lo = mid;
+        else hi = mid;
+    }
+    col[p] = int32_t(lo);
+    iota[p] = int32_t(p);
+    const int32_t r = inner[p];
+    if (r < 0 || r >= rows) atomicOr(flags, 2);
+    else atomicAdd(rowcount + r, 1);
+}
+
+template <class S>
+__global__ void csc_gather_kernel(const int32_t* __restrict__ perm, const int32_t* __restrict__ col,
+                                  const S* __restrict__ cvals, int64_t nnz, int32_t* __restrict__ colidx,
+                                  S* __restrict__ vals) {
+    const int64_t k = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k >= nnz) return;
+    const int32_t p = perm[k];
+    colidx[k] = col[p];
+    vals[k] = cvals[p];
+}
+
+// Row-length statistics on the device (what plan.hpp: row_stats computes on the host).
+// out[0] = max len, out[1] = min len, out[2..3] = padded entries of 64-row slices (u64), dsum[0] = sum (len-mean)^2
+__global__ void row_stats_kernel(const int32_t* __restrict__ rowptr, int64_t rows, double mean, int* imax, int* imin,
+                                 unsigned long long* padded, double* var) {
+    // one thread per 64-row slice
+    const int64_t sl = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const int64_t r0 = sl * 64;
+    if (r0 >= rows) return;
+    const int64_t r1 = r0 + 64 < rows ? r0 + 64 : rows;
+    int mx = 0, mn = INT32_MAX;
+    double v = 0.0;
+    int32_t prev = rowptr[r0];
+    for (int64_t r = r0; r < r1; ++r) {
+        const int32_t nx = rowptr[r + 1];
+        const int len = nx - prev;
+        prev = nx;
+        mx = len > mx ? len : mx;
+        mn = len < mn ? len : mn;
+        const double d = len - mean;
+        v += d * d;
+    }
+    atomicMax(imax, mx);
+    atomicMin(imin, mn);
+    atomicAdd(padded, (unsigned long long)mx * 64ull);
+    atomicAdd(var, v);
+}
+
+}  // namespace eigsol_b200
