@@ -65,7 +65,9 @@ enum {
     EIGSOL_B200_KERNEL_CSR_VECTOR = 2, /* CSR, 2..32 lanes per row (32 = warp per row)                  */
     EIGSOL_B200_KERNEL_CSR_STREAM = 3, /* CSR, nnz streamed through shared memory, rows reduced there   */
     EIGSOL_B200_KERNEL_SELL = 4,       /* sliced layout built from the CSR (slice = 32 lanes x R rows)  */
-    EIGSOL_B200_KERNEL_GEMV = 5        /* dense column-major GEMV                                       */
+    EIGSOL_B200_KERNEL_GEMV = 5,       /* dense column-major GEMV                                       */
+    EIGSOL_B200_KERNEL_CSR_WINDOW = 6  /* CSR, thread per row, x window of each row block staged in shared
+                                          memory by one TMA bulk copy (banded / stencil matrices)       */
 };
 
 typedef struct eigsol_b200_matrix eigsol_b200_matrix; /* device-resident matrix + iteration state */

@@ -21,7 +21,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _capi
-from ._capi import (C128, F64, KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_STREAM, KERNEL_CSR_VECTOR, KERNEL_GEMV,
+from ._capi import (C128, F64, KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_STREAM, KERNEL_CSR_VECTOR, KERNEL_CSR_WINDOW, KERNEL_GEMV,
                     KERNEL_NAMES, KERNEL_SELL, EigsolB200Error)
 
 __all__ = ["Matrix", "SolverOptions", "EigenResult", "powerMethod", "power_method", "DeviceMatrix", "Comm",

@@ -16,8 +16,8 @@ LIB_PATH = os.path.join(_HERE, "libeigsol_b200.so")
 
 OK, ERR_INVALID, ERR_NOT_SQUARE, ERR_ZERO_SIZE, ERR_DEVICE, ERR_STATE = range(6)
 F64, C128 = 0, 1
-KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_VECTOR, KERNEL_CSR_STREAM, KERNEL_SELL, KERNEL_GEMV = range(6)
-KERNEL_NAMES = {0: "auto", 1: "csr_scalar", 2: "csr_vector", 3: "csr_stream", 4: "sell", 5: "gemv"}
+KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_VECTOR, KERNEL_CSR_STREAM, KERNEL_SELL, KERNEL_GEMV, KERNEL_CSR_WINDOW = range(7)
+KERNEL_NAMES = {0: "auto", 1: "csr_scalar", 2: "csr_vector", 3: "csr_stream", 4: "sell", 5: "gemv", 6: "csr_window"}
 
 # every symbol include/eigsol_b200.h declares (tests check the library exports all of them)
 EXPORTS = [

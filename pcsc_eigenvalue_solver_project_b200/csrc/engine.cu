@@ -149,6 +149,8 @@ struct MatrixImpl {
     DevBuf d_rowblk;
     std::vector<int32_t> rowblk_h;
     int nblk = 0;
+    DevBuf d_window;    // CSR_WINDOW: per 256-row unit {first column, count} staged by the TMA bulk copy
+    int window_smem = 0;  // dynamic shared memory of the window kernel (bytes)
     DevBuf d_deferred;  // MODE_PEER: per work unit of the chosen kernel, 1 = reads halo entries
     bool have_deferred = false;
     int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
@@ -457,7 +459,7 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
     const int forced = env_int("EIGSOL_B200_KERNEL", 0);
     const KernelChoice ch = choose_kernel(dtype, stats);
-    if (forced > 0 && forced <= K_SELL) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
+    if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
     else set_kernel(ch.kernel, ch.lanes);
 }
 
@@ -566,7 +568,7 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         stats.sell_fill = double(padded) / double(nnz);
     }
     const int forced = env_int("EIGSOL_B200_KERNEL", 0);
-    if (forced > 0 && forced <= K_SELL) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
+    if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
     else set_kernel(K_AUTO, 0);
 }
 
@@ -605,7 +607,7 @@ void MatrixImpl::set_kernel(int kernel_, int lanes_) {
         kernel_ = ch.kernel;
         lanes_ = ch.lanes;
     }
-    if (kernel_ < K_CSR_SCALAR || kernel_ > K_SELL) throw PlanError("unknown sparse kernel id");
+    if ((kernel_ < K_CSR_SCALAR || kernel_ > K_SELL) && kernel_ != K_CSR_WINDOW) throw PlanError("unknown sparse kernel id");
     if (kernel_ == K_CSR_VECTOR) {
         if (lanes_ == 0) lanes_ = 8;
         if (lanes_ != 2 && lanes_ != 4 && lanes_ != 8 && lanes_ != 16 && lanes_ != 32)
@@ -639,6 +641,49 @@ void MatrixImpl::set_kernel(int kernel_, int lanes_) {
             d_rowblk.upload(rb.data(), sizeof(int32_t) * rb.size(), stream);
             EIGSOL_CUDA(cudaStreamSynchronize(stream));
         }
+    } else if (kernel_ == K_CSR_WINDOW) {
+        // per unit of 256 rows: the contiguous range of LOCAL columns its rows reference, 16-byte aligned and
+        // truncated to the shared-memory budget; halo columns and outliers are gathered from global memory
+        lanes_ = 0;
+        ensure_host_csr();
+        const int B = 256;
+        const int64_t per16 = 16 / ss();  // elements per 16 bytes
+        const int64_t budget = (int64_t(env_int("EIGSOL_B200_WINDOW_KB", 64)) << 10) / ss();
+        const int64_t nunits = (nloc + B - 1) / B;
+        std::vector<int32_t> w(size_t(std::max<int64_t>(nunits, 1)) * 2, 0);
+        int64_t maxcount = 0;
+        for (int64_t u = 0; u < nunits; ++u) {
+            const int64_t r0 = u * B, r1 = std::min<int64_t>(r0 + B, nloc);
+            int64_t cmin = INT64_MAX, cmax = -1;
+            for (int32_t p = csr.rowptr[size_t(r0)]; p < csr.rowptr[size_t(r1)]; ++p) {
+                const int64_t c = csr.colidx[size_t(p)];
+                if (c >= nloc_pad) continue;  // halo entry
+                cmin = std::min(cmin, c);
+                cmax = std::max(cmax, c);
+            }
+            if (cmax < 0) continue;
+            // centre a too-wide window on the unit's own rows (the diagonal band)
+            int64_t first = cmin / per16 * per16;
+            int64_t count = (cmax + 1 - first + per16 - 1) / per16 * per16;
+            if (count > budget) {
+                const int64_t mid = (r0 + r1) / 2;
+                first = std::max<int64_t>(cmin, mid - budget / 2) / per16 * per16;
+                count = budget / per16 * per16;
+            }
+            count = std::min<int64_t>(count, (nloc_pad - first) / per16 * per16);
+            if (count <= 0) continue;
+            w[size_t(u) * 2] = int32_t(first);
+            w[size_t(u) * 2 + 1] = int32_t(count);
+            maxcount = std::max(maxcount, count);
+        }
+        window_smem = int(std::max<int64_t>(maxcount * ss(), 16));
+        d_window.alloc(sizeof(int32_t) * w.size());
+        d_window.upload(w.data(), sizeof(int32_t) * w.size(), stream);
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        if (dtype)
+            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, window_smem));
+        else
+            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, window_smem));
     } else {
         lanes_ = 0;
     }
@@ -699,15 +744,16 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
 // -------------------------------------------------------------------------------------------------
 // Launch configuration: persistent grids sized from the SM count and the kernel's occupancy.
 // -------------------------------------------------------------------------------------------------
-template <class K> static int occupancy(K kern, int block) {
+template <class K> static int occupancy(K kern, int block, size_t smem = 0) {
     int nb = 0;
-    EIGSOL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, block, 0));
+    EIGSOL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, block, smem));
     return std::max(nb, 1);
 }
 
-template <class S> static int sparse_occupancy(int kernel, int lanes) {
+template <class S> static int sparse_occupancy(int kernel, int lanes, int window_smem) {
     constexpr int B = 256;
     switch (kernel) {
+        case K_CSR_WINDOW: return occupancy(spmv_csr_window_kernel<S, B>, B, size_t(window_smem));
         case K_CSR_SCALAR: return occupancy(spmv_csr_scalar_kernel<S, B>, B);
         case K_CSR_STREAM: return occupancy(spmv_csr_stream_kernel<S, B>, B);
         case K_SELL:
@@ -739,10 +785,11 @@ void MatrixImpl::configure_launch() {
         d_tile_ticket.alloc(sizeof(unsigned) * size_t(ntiles));
         stored_bytes = s * lda * ext_len + s * (ext_len + nloc) + 2 * s * int64_t(nseg) * lda;
     } else {
-        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes) : sparse_occupancy<double>(kernel, lanes);
+        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes, window_smem) : sparse_occupancy<double>(kernel, lanes, window_smem);
         const int resident = sm_count * occ;
         int64_t need = 1;
         switch (kernel) {
+            case K_CSR_WINDOW:
             case K_CSR_SCALAR: need = (nloc + block - 1) / block; break;
             case K_CSR_VECTOR: need = (nloc * lanes + block - 1) / block; break;
             case K_CSR_STREAM: need = nblk; break;
@@ -771,6 +818,7 @@ void MatrixImpl::build_deferred() {
     (void)unit_of_row;
     std::vector<int64_t> unit_first;  // first row of each unit (+ end)
     switch (kernel) {
+        case K_CSR_WINDOW:
         case K_CSR_SCALAR: nunits = (nloc + block - 1) / block; break;
         case K_CSR_VECTOR: nunits = (nloc + (block / lanes) - 1) / (block / lanes); break;
         case K_CSR_STREAM: nunits = nblk; break;
@@ -786,6 +834,7 @@ void MatrixImpl::build_deferred() {
     for (int64_t u = 0; u < nunits; ++u) {
         int64_t r0, r1;
         switch (kernel) {
+            case K_CSR_WINDOW:
             case K_CSR_SCALAR: r0 = u * block; r1 = r0 + block; break;
             case K_CSR_VECTOR: r0 = u * (block / lanes); r1 = r0 + block / lanes; break;
             case K_CSR_STREAM: r0 = rowblk_h[size_t(u)]; r1 = rowblk_h[size_t(u) + 1]; break;
@@ -822,11 +871,11 @@ void MatrixImpl::build_deferred() {
 // ping-pong buffer from the device state), which is what lets a CUDA graph of them be replayed.
 // Kernel launch with the programmatic-stream-serialization attribute (PDL) when enabled.
 template <class... KArgs, class... Args>
-static void launch_pdl(bool pdl, cudaStream_t st, void (*kern)(KArgs...), dim3 g, dim3 b, Args... args) {
+static void launch_pdl(bool pdl, cudaStream_t st, void (*kern)(KArgs...), dim3 g, dim3 b, size_t smem, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = g;
     cfg.blockDim = b;
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -843,22 +892,25 @@ template <class S> static void launch_sparse(MatrixImpl& m, int ph) {
     const dim3 g(m.grid), b(B);
     cudaStream_t st = m.stream;
     switch (m.kernel) {
-        case K_CSR_SCALAR: launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B>, g, b, A, it, ph); break;
-        case K_CSR_STREAM: launch_pdl(m.pdl, st, spmv_csr_stream_kernel<S, B>, g, b, A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
+        case K_CSR_SCALAR: launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B>, g, b, 0, A, it, ph); break;
+        case K_CSR_WINDOW:
+            launch_pdl(m.pdl, st, spmv_csr_window_kernel<S, B>, g, b, size_t(m.window_smem), A, m.d_window.as<int2>(), it, ph);
+            break;
+        case K_CSR_STREAM: launch_pdl(m.pdl, st, spmv_csr_stream_kernel<S, B>, g, b, 0, A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
         case K_SELL: {
             SellView<S> V{int32_t(m.nloc), int32_t(m.sell_nslices), m.d_sell_off.as<int64_t>(), m.d_sell_col.as<int32_t>(),
                           m.d_sell_val.as<S>()};
-            if (m.lanes == 2) launch_pdl(m.pdl, st, spmv_sell_kernel<S, 2, B>, g, b, V, it, ph);
-            else launch_pdl(m.pdl, st, spmv_sell_kernel<S, 1, B>, g, b, V, it, ph);
+            if (m.lanes == 2) launch_pdl(m.pdl, st, spmv_sell_kernel<S, 2, B>, g, b, 0, V, it, ph);
+            else launch_pdl(m.pdl, st, spmv_sell_kernel<S, 1, B>, g, b, 0, V, it, ph);
             break;
         }
         case K_CSR_VECTOR:
             switch (m.lanes) {
-                case 2: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 2, B>, g, b, A, it, ph); break;
-                case 4: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 4, B>, g, b, A, it, ph); break;
-                case 8: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 8, B>, g, b, A, it, ph); break;
-                case 16: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 16, B>, g, b, A, it, ph); break;
-                default: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 32, B>, g, b, A, it, ph); break;
+                case 2: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 2, B>, g, b, 0, A, it, ph); break;
+                case 4: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 4, B>, g, b, 0, A, it, ph); break;
+                case 8: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 8, B>, g, b, 0, A, it, ph); break;
+                case 16: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 16, B>, g, b, 0, A, it, ph); break;
+                default: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 32, B>, g, b, 0, A, it, ph); break;
             }
             break;
         default: throw StateError("no sparse kernel selected");
@@ -870,7 +922,7 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
-    launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B>, dim3(m.grid), dim3(B), A, it, ph);
+    launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B>, dim3(m.grid), dim3(B), 0, A, it, ph);
 }
 
 void MatrixImpl::launch_matvec(int phase) {

@@ -756,6 +756,93 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
 }
 
 // =================================================================================================
+// CSR with the x window of a row block staged in shared memory by the TMA engine ("where locality
+// allows": banded / stencil matrices).  The host records for every unit of BLOCK rows the contiguous range
+// [first, first+count) of local columns its rows reference (truncated to the shared-memory budget); one
+// elected thread issues a single bulk copy (cp.async.bulk, completion on an mbarrier) of that range of v
+// while all threads fetch their row pointers; products then read x from shared memory, and any column
+// outside the window (halo entries, outliers) falls back to a global gather.  One thread per row.
+// =================================================================================================
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_addr(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_addr(bar)), "r"(parity)
+            : "memory");
+    }
+}
+
+template <class S, int BLOCK>
+__global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, const int2* __restrict__ win, IterArgs<S> it,
+                                                                int phase) {
+    extern __shared__ __align__(128) unsigned char window_smem[];
+    __shared__ __align__(8) unsigned long long bar;
+    __shared__ SendSm sends;
+    pdl_prologue();
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
+        return;
+    }
+    LaunchCtx c;
+    if (!launch_begin<S>(it, phase, c)) return;
+    if (threadIdx.x == 0) mbar_init(&bar, 1);
+    load_sends<S>(it, c, sends);  // ends with a CTA barrier: the mbarrier is initialised for everyone
+    S* xs = reinterpret_cast<S*>(window_smem);
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    double are = 0.0, aim = 0.0, qn = 0.0;
+    unsigned parity = 0;
+    const int nunits = (A.rows + BLOCK - 1) / BLOCK;
+    walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nunits, [&](int unit) {
+        const int2 w = __ldg(win + unit);  // {first column, count}; 16-byte aligned range, count may be 0
+        if (w.y > 0 && threadIdx.x == 0) tma_load_1d(xs, u + w.x, unsigned(w.y) * unsigned(sizeof(S)), &bar);
+        const int row = unit * BLOCK + threadIdx.x;
+        int p0 = 0, p1 = 0;
+        if (row < A.rows) {
+            p0 = __ldg(A.rowptr + row);
+            p1 = __ldg(A.rowptr + row + 1);
+        }
+        if (w.y > 0) {
+            mbar_wait(&bar, parity);
+            parity ^= 1u;
+        }
+        if (row < A.rows) {
+            S acc = Sc<S>::zero();
+            for (int p = p0; p < p1; ++p) {
+                const int col = __ldg(A.colidx + p);
+                const unsigned k = unsigned(col - w.x);
+                const S x = k < unsigned(w.y) ? xs[k] : Sc<S>::ldg(u + col);
+                Sc<S>::mac(acc, __ldg(A.vals + p), x);
+            }
+            const unsigned kd = unsigned(row - w.x);
+            const S own = kd < unsigned(w.y) ? xs[kd] : Sc<S>::ldg(u + row);
+            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), own, out, row, are, aim, qn);
+        }
+        __syncthreads();  // everyone is done reading the window before the next bulk copy lands in it
+    });
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
+}
+
+// =================================================================================================
 // SELL: a warp owns a slice of 32*R consecutive rows, lane l the R rows  slice*32R + l*R + {0..R-1}.
 // Entry j of those rows is stored at  slice_off + (j*32 + l)*R : one warp instruction reads 32*R
 // consecutive values (R=2, f64: 16-byte loads; c128: 16 bytes per value) and 32*R consecutive column

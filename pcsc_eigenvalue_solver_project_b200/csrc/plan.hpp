@@ -146,7 +146,7 @@ inline RowStats row_stats(int64_t rows, const int32_t* rowptr) {
 }
 
 // Kernel ids mirror include/eigsol_b200.h.
-enum KernelId { K_AUTO = 0, K_CSR_SCALAR = 1, K_CSR_VECTOR = 2, K_CSR_STREAM = 3, K_SELL = 4, K_GEMV = 5 };
+enum KernelId { K_AUTO = 0, K_CSR_SCALAR = 1, K_CSR_VECTOR = 2, K_CSR_STREAM = 3, K_SELL = 4, K_GEMV = 5, K_CSR_WINDOW = 6 };
 
 struct KernelChoice {
     int kernel = K_CSR_SCALAR;

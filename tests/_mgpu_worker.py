@@ -58,7 +58,7 @@ def main():
     if np.max(np.abs(y - yref)) > 1e-14 * np.max(np.abs(yref)):
         failures.append("lap3d matvec")
     check("lap3d fixed", dm.power(x0, es.SolverOptions(50, -1.0)), orc.power_csc((n, n), rp, ci, v, x0, 50, -1.0))
-    for kernel, lanes in [(es.KERNEL_SELL, 2), (es.KERNEL_CSR_STREAM, 0), (es.KERNEL_CSR_VECTOR, 4)]:
+    for kernel, lanes in [(es.KERNEL_SELL, 2), (es.KERNEL_CSR_STREAM, 0), (es.KERNEL_CSR_VECTOR, 4), (es.KERNEL_CSR_WINDOW, 0)]:
         dm.set_kernel(kernel, lanes)
         check(f"lap3d k{kernel}", dm.power(x0, es.SolverOptions(20, -1.0)), orc.power_csc((n, n), rp, ci, v, x0, 20, -1.0))
     dm.close()

@@ -50,7 +50,7 @@ def check_result(r, ref, fixed_trips=True):
 SPARSE_VARIANTS = [
     (es.KERNEL_CSR_SCALAR, 0), (es.KERNEL_CSR_VECTOR, 2), (es.KERNEL_CSR_VECTOR, 4), (es.KERNEL_CSR_VECTOR, 8),
     (es.KERNEL_CSR_VECTOR, 16), (es.KERNEL_CSR_VECTOR, 32), (es.KERNEL_CSR_STREAM, 0), (es.KERNEL_SELL, 1),
-    (es.KERNEL_SELL, 2),
+    (es.KERNEL_SELL, 2), (es.KERNEL_CSR_WINDOW, 0),
 ]
 
 

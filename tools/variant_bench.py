@@ -14,7 +14,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import pcsc_eigenvalue_solver_project_b200 as es
 from pcsc_eigenvalue_solver_project_b200 import generators as gen
 
-VARIANTS = [(es.KERNEL_SELL, 2), (es.KERNEL_SELL, 1), (es.KERNEL_CSR_STREAM, 0), (es.KERNEL_CSR_SCALAR, 0),
+VARIANTS = [(es.KERNEL_CSR_WINDOW, 0), (es.KERNEL_SELL, 2), (es.KERNEL_SELL, 1), (es.KERNEL_CSR_STREAM, 0), (es.KERNEL_CSR_SCALAR, 0),
             (es.KERNEL_CSR_VECTOR, 2), (es.KERNEL_CSR_VECTOR, 4), (es.KERNEL_CSR_VECTOR, 8),
             (es.KERNEL_CSR_VECTOR, 16), (es.KERNEL_CSR_VECTOR, 32)]
 
