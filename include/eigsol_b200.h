@@ -185,6 +185,13 @@ EIGSOL_B200_API int eigsol_b200_power_end(eigsol_b200_matrix* m, void* x_out, do
  * vectors.  Used by the parity tests to check every kernel variant element-wise. */
 EIGSOL_B200_API int eigsol_b200_matvec(eigsol_b200_matrix* m, const void* x, void* y);
 
+/* dot_out = x^H (A x) (conjugated, eigen/Eigen/src/Core/InnerProduct.h:255), *norm2_out = ||A x||^2, from ONE
+ * fused launch on the resident matrix: the Rayleigh-quotient step `x.dot(A * x)` of the reference's shifted
+ * inverse method (src/power_method/shifted_inverse_power_solver.hpp:62), whose LU solve stays host code.
+ * x is a GLOBAL length-n host vector on every rank; either output may be NULL. */
+EIGSOL_B200_API int eigsol_b200_rayleigh(eigsol_b200_matrix* m, const void* x, double dot_out[2],
+                                         double* norm2_out);
+
 /* Total kernel launches this handle has issued (bench.py's gpu_launches claim). */
 EIGSOL_B200_API int64_t eigsol_b200_matrix_launch_count(const eigsol_b200_matrix* m);
 

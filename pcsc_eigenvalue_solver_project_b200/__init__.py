@@ -315,6 +315,15 @@ class DeviceMatrix:
         _capi.check(_capi.lib().eigsol_b200_matvec(self._h, _capi.ptr(self._vec(x)), _capi.ptr(y)))
         return y
 
+    def rayleigh(self, x):
+        """``(x^H A x, ||A x||^2)`` from one fused launch: the ``x.dot(A * x)`` step of the reference's shifted
+        inverse method (src/power_method/shifted_inverse_power_solver.hpp:62)."""
+        dot = (C.c_double * 2)()
+        nrm = C.c_double()
+        _capi.check(_capi.lib().eigsol_b200_rayleigh(self._h, _capi.ptr(self._vec(x)), dot, C.byref(nrm)))
+        d = complex(dot[0], dot[1])
+        return (d if np.issubdtype(self.dtype, np.complexfloating) else d.real), float(nrm.value)
+
     def close(self):
         if self._h:
             _capi.lib().eigsol_b200_matrix_destroy(self._h)

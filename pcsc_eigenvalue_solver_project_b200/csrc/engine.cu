@@ -225,6 +225,7 @@ struct MatrixImpl {
     void gather_download(const void* d_local, void* host_out);
     void run(const void* x0, int max_it, double tol, void* x_out, double lambda_out[2], int* iters, int* conv);
     void matvec(const void* x, void* y);
+    void rayleigh(const void* x, double out[4]);
     void fill_info(eigsol_b200_matrix_info* info) const;
 };
 
@@ -1172,6 +1173,20 @@ void MatrixImpl::matvec(const void* x, void* y) {
     begun = false;
 }
 
+// x^H (A x) and ||A x||^2 in one fused launch (the Rayleigh-quotient step of the reference's shifted inverse
+// method, src/power_method/shifted_inverse_power_solver.hpp:62, `x.dot(A * x)`): launch 0 of the loop with
+// sigma = 1 leaves exactly these sums; the control-only launch folds them into the state.
+void MatrixImpl::rayleigh(const void* x, double out[4]) {
+    begin(x, 1, -1.0);
+    issue_trips(1);
+    const PowerState st = poll_state();
+    out[0] = st.last_a[0];
+    out[1] = st.last_a[1];
+    out[2] = st.q[1];
+    out[3] = 0.0;
+    begun = false;
+}
+
 void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
     std::memset(info, 0, sizeof *info);
     info->dtype = dtype;
@@ -1448,6 +1463,21 @@ int eigsol_b200_matvec(eigsol_b200_matrix* m, const void* x, void* y) {
     std::lock_guard<std::mutex> lock(g_api_mutex);
     return guarded([&] {
         m->impl.matvec(x, y);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_rayleigh(eigsol_b200_matrix* m, const void* x, double dot_out[2], double* norm2_out) {
+    if (!m || !x) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        double o[4];
+        m->impl.rayleigh(x, o);
+        if (dot_out) {
+            dot_out[0] = o[0];
+            dot_out[1] = o[1];
+        }
+        if (norm2_out) *norm2_out = o[2];
         return int(EIGSOL_B200_OK);
     });
 }

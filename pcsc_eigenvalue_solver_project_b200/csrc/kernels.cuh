@@ -169,6 +169,7 @@ struct PowerState {
     double q[kRing];       // ||v_m||^2 at slot m % 3
     double sigma[kRing];   // sigma_m at slot m % 3
     double final_q;        // ||v||^2 of the buffer holding the result vector
+    double last_a[2];      // v^H (sigma A v) of the launch folded last (eigsol_b200_rayleigh reads it)
     unsigned long long flag_base;  // peer flags of this solve are flag_base + launch number (never reset: monotonic)
     int max_trips;         // opts.maxIterations
     int launch_no;         // launches executed since begin (the next launch is number launch_no)
@@ -197,6 +198,8 @@ __device__ __forceinline__ bool close_relative(double are, double aim, double br
 __device__ __forceinline__ void fold_launch(PowerState* st, int j, double are, double aim, double qn) {
     const int r = j % kRing;
     st->q[(j + 1) % kRing] = qn;
+    st->last_a[0] = are;
+    st->last_a[1] = aim;
     if (j >= 1) {
         const double denom = st->sigma[r] * st->q[r];
         const double lre = are / denom, lim = aim / denom;

@@ -351,3 +351,27 @@ def test_device_ingest_rejects_malformed():
     with pytest.raises(ValueError, match="not monotone"):
         es.DeviceMatrix.from_matrix(es.Matrix(((2, 2), np.array([0, 2, 1], dtype=np.int32),
                                                np.array([0, 1], dtype=np.int32), vals)))
+
+
+# ---- Rayleigh-quotient step of the shifted inverse method (shifted_inverse_power_solver.hpp:62) --------
+@pytest.mark.parametrize("cplx", [False, True])
+def test_rayleigh_step_sparse_and_dense(orc, cplx):
+    n = 700
+    dt = np.complex128 if cplx else np.float64
+    rowptr, colidx, vals = gen.random_sparse_csr(n, 7.0, seed=31, complex_values=cplx, skew=5.0, diag_boost=3.0)
+    outer, inner, cv = general_csc(n, rowptr, colidx, vals)
+    x = orc.random_unit(n, dt, seed=12)
+    y = orc.spmv_csc((n, n), outer, inner, cv, x)
+    dm = es.DeviceMatrix.from_matrix(es.Matrix(((n, n), outer, inner, cv)))
+    dot, nrm2 = dm.rayleigh(x)
+    assert abs(dot - np.vdot(x, y)) <= 1e-12 * max(1.0, abs(np.vdot(x, y)))   # x.dot(A*x) conjugates x
+    assert abs(nrm2 - np.vdot(y, y).real) <= 1e-12 * np.vdot(y, y).real
+    dm.close()
+    a = gen.dense_random_hermitian(64, seed=5) if cplx else gen.dense_random_symmetric(64, seed=5)
+    x = orc.random_unit(64, dt, seed=13)
+    dm = es.DeviceMatrix.from_matrix(es.Matrix(a))
+    dot, nrm2 = dm.rayleigh(x)
+    y = a @ x
+    assert abs(dot - np.vdot(x, y)) <= 1e-12 * max(1.0, abs(np.vdot(x, y)))
+    assert abs(nrm2 - np.vdot(y, y).real) <= 1e-12 * np.vdot(y, y).real
+    dm.close()
