@@ -179,7 +179,7 @@ def run_reference_arm(args, rank, world):
         cb = reference_rate(args.workload, budget_s=float(os.environ.get("BENCH_REF_BUDGET_S", 45)),
                             max_trips=max(1, args.steps))
     except Exception as e:  # the oracle always exists; this is a packaging error worth seeing
-        print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"}))
+        emit({"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"})
         return
     line = {"impl": "reference", "metric": "power_iterations_per_s", "value": cb["value"], "unit": "iter/s",
             "n_gpus": args.gpus, "steps": cb["trips"], "warmup": 1, "ms_per_step": 1e3 / cb["value"],
@@ -188,11 +188,34 @@ def run_reference_arm(args, rank, world):
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Library chatter (NCCL prints its version banner on stdout) must not reach the ONE JSON line the
+    contract asks for: fd 1 is pointed at stderr for the run and emit() writes to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -351,7 +374,7 @@ def main():
                        "grid": info["grid"], "block": info["block"], "halo_per_rank": info["halo"]},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches,
             "clocks": clocks, "lambda": repr(res.eigenvalue), "trips_done": res.iterations, "build_s": round(t_build, 2)}
-    print(json.dumps(line))
+    emit(line)
     dm.close()
     if dist is not None:
         dist.destroy_process_group()

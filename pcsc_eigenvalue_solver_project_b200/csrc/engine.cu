@@ -432,17 +432,22 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     hi = row_begin[rank + 1];
     nloc = hi - lo;
     if (a.rows != nloc) throw PlanError("row block size does not match the partition");
+    Trace tr;
     csr = std::move(a);
     local_nnz = csr.nnz();
     halo = halo_plan(nloc, csr.rowptr.data(), csr.colidx.data(), row_begin, rank);
     nhalo = int64_t(halo.cols.size());
+    tr.mark("rows: halo plan");
     alloc_vectors();
     if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
     localize_columns(local_nnz, csr.colidx.data(), lo, hi, nloc_pad, halo.cols);
     csr.cols = ext_len;
+    tr.mark("rows: vectors + localize");
     plan_exchange();
     setup_peer();
+    tr.mark("rows: exchange plan + peer map");
     stats = row_stats(nloc, csr.rowptr.data());
+    tr.mark("rows: row stats");
     if (nranks > 1) {
         const std::vector<int64_t> all = comm_allgather_i64(comm, local_nnz);
         nnz_global = 0;
@@ -458,6 +463,7 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     d_vals.alloc(size_t(std::max<int64_t>(local_nnz, 1)) * ss());
     d_vals.upload(csr.vals.data(), size_t(local_nnz) * ss(), stream);
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    tr.mark("rows: upload");
     const int forced = env_int("EIGSOL_B200_KERNEL", 0);
     const KernelChoice ch = choose_kernel(dtype, stats);
     if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
