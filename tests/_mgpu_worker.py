@@ -99,6 +99,37 @@ def main():
         failures.append("zero iterations")
     dm.close()
 
+    # 5. Rayleigh step on the sharded matrix, and repeated solves on one handle (flag epochs keep counting)
+    g = 20
+    n = g ** 3
+    rp, ci, v = gen.laplacian_3d(g)
+    lo, hi = n * rank // world, n * (rank + 1) // world
+    rpl, cil, vl = gen.laplacian_3d(g, lo, hi)
+    x0 = orc.random_unit(n, np.float64, seed=7)
+    dm = es.DeviceMatrix.from_csr_rows(n, lo, rpl, cil, vl, comm)
+    y = orc.spmv_csc((n, n), rp, ci, v, x0)
+    dot, nrm2 = dm.rayleigh(x0)
+    if abs(dot - np.vdot(x0, y)) > 1e-12 or abs(nrm2 - np.vdot(y, y)) > 1e-12 * np.vdot(y, y):
+        failures.append("rayleigh")
+    ref = orc.power_csc((n, n), rp, ci, v, x0, 17, -1.0)
+    for rep in range(3):
+        check(f"repeat {rep}", dm.power(x0, es.SolverOptions(17, -1.0)), ref)
+
+    # 6. a peer that stops taking part must surface as an error on the others, never as a hang (peer mode only)
+    if os.environ.get("EIGSOL_B200_EXPECT_EXCHANGE") == "peer":
+        dm.begin(x0, 1000, -1.0)  # collective
+        if rank == 0:
+            try:
+                dm.step(40)
+                dm.end(want_vector=False)
+                failures.append("missing peer not detected")
+            except es.EigsolB200Error as e:
+                if "did not signal" not in str(e):
+                    failures.append(f"unexpected error text: {e}")
+                print(f"[missing peer] rank 0 got the expected error: {e}", flush=True)
+        dist.barrier()
+    dm.close()
+
     flag = torch.tensor([len(failures)], device="cuda")
     dist.all_reduce(flag)
     comm.close()

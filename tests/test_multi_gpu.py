@@ -20,6 +20,7 @@ def test_row_sharded_power_iteration(world, exchange):
     port = 29500 + world + (20 if exchange == "nccl" else 0)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "_mgpu_worker.py")]
-    env = dict(os.environ, EIGSOL_B200_EXCHANGE=exchange, EIGSOL_B200_EXPECT_EXCHANGE=exchange)
+    env = dict(os.environ, EIGSOL_B200_EXCHANGE=exchange, EIGSOL_B200_EXPECT_EXCHANGE=exchange,
+               EIGSOL_B200_PEER_TIMEOUT_MS="1500")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-4000:]
