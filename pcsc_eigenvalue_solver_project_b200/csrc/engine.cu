@@ -192,6 +192,7 @@ struct MatrixImpl {
     void init_sparse_local(CsrHost&& local_global_cols);
     void init_sparse_device_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner, const void* values);
     void ensure_host_csr();
+    void init_sparse_device_rows(const int32_t* rowptr, const int32_t* colidx, const void* values);
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
     void plan_exchange();
     void setup_peer();
@@ -579,6 +580,133 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
     else set_kernel(K_AUTO, 0);
 }
 
+// -------------------------------------------------------------------------------------------------
+// Row block [lo, hi) in CSR with GLOBAL columns (each rank of a multi-GPU run, or the whole matrix on one
+// GPU): staged upload straight from the caller's arrays, then halo discovery, column renumbering and row
+// statistics on the device (ingest.cuh).  row_begin must be set.
+// -------------------------------------------------------------------------------------------------
+void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* colidx, const void* values) {
+    Trace tr;
+    dense = false;
+    lo = row_begin[rank];
+    hi = row_begin[rank + 1];
+    nloc = hi - lo;
+    if (n > INT32_MAX) throw PlanError("matrix dimension exceeds int32 indices");
+    if (!rowptr) throw PlanError("null rowptr");
+    if (rowptr[0] != 0) throw PlanError("CSR rowptr must start at 0");
+    for (int64_t i = 0; i < nloc; ++i)
+        if (rowptr[i + 1] < rowptr[i]) throw PlanError("CSR rowptr not monotone");
+    const int64_t nnz = rowptr[nloc];
+    if (nnz > 0 && (!colidx || !values)) throw PlanError("null colidx");
+    local_nnz = nnz;
+    const size_t s = size_t(ss());
+    const size_t nz = size_t(std::max<int64_t>(nnz, 1));
+    d_rowptr.alloc(sizeof(int32_t) * size_t(nloc + 1));
+    d_colidx.alloc(sizeof(int32_t) * nz);
+    d_vals.alloc(nz * s);
+    StagedUploader up;
+    up.add(d_rowptr.p, rowptr, sizeof(int32_t) * size_t(nloc + 1));
+    up.add(d_colidx.p, colidx, sizeof(int32_t) * size_t(nnz));
+    up.add(d_vals.p, values, size_t(nnz) * s);
+    EIGSOL_CUDA(up.run(device, env_int("EIGSOL_B200_UPLOAD_THREADS", 2)));
+    tr.mark("rows(dev): staged upload");
+    const int B = 256;
+    const unsigned gnz = unsigned((std::max<int64_t>(nnz, 1) + B - 1) / B);
+    const unsigned gn = unsigned((std::max<int64_t>(n, 1) + B - 1) / B);
+    DevBuf d_mark, d_pos, d_flags, d_tmp, d_hcols;
+    d_flags.alloc(64);
+    halo = HaloPlan();
+    halo.peer_count.assign(size_t(nranks), 0);
+    halo.peer_off.assign(size_t(nranks) + 1, 0);
+    if (nnz > 0) {
+        d_mark.alloc(sizeof(int32_t) * size_t(n));
+        d_pos.alloc(sizeof(int32_t) * size_t(n));
+        rows_mark_kernel<<<gnz, B, 0, stream>>>(d_colidx.as<int32_t>(), nnz, n, lo, hi, d_mark.as<int32_t>(), d_flags.as<int>());
+        size_t tb = 0;
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, d_mark.as<int32_t>(), d_pos.as<int32_t>(), int(n), stream));
+        d_tmp.alloc(tb);
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp.p, tb, d_mark.as<int32_t>(), d_pos.as<int32_t>(), int(n), stream));
+        int32_t last[2] = {0, 0};
+        int hflags = 0;
+        EIGSOL_CUDA(cudaMemcpyAsync(&last[0], d_mark.as<int32_t>() + (n - 1), sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaMemcpyAsync(&last[1], d_pos.as<int32_t>() + (n - 1), sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaMemcpyAsync(&hflags, d_flags.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        if (hflags & 2) throw PlanError("CSR column index out of range");
+        nhalo = int64_t(last[0]) + int64_t(last[1]);
+        halo.cols.resize(size_t(nhalo));
+        if (nhalo > 0) {
+            d_hcols.alloc(sizeof(int32_t) * size_t(nhalo));
+            halo_compact_kernel<<<gn, B, 0, stream>>>(d_mark.as<int32_t>(), d_pos.as<int32_t>(), n, d_hcols.as<int32_t>());
+            EIGSOL_CUDA(cudaMemcpyAsync(halo.cols.data(), d_hcols.p, sizeof(int32_t) * size_t(nhalo), cudaMemcpyDeviceToHost, stream));
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+            // owners of the (sorted) halo columns
+            size_t k = 0;
+            for (int q = 0; q < nranks; ++q) {
+                const size_t k0 = k;
+                while (k < halo.cols.size() && halo.cols[k] < row_begin[size_t(q) + 1]) ++k;
+                halo.peer_count[size_t(q)] = int64_t(k - k0);
+            }
+            for (int q = 0; q < nranks; ++q) halo.peer_off[size_t(q) + 1] = halo.peer_off[size_t(q)] + halo.peer_count[size_t(q)];
+        }
+        launches += 2;
+    } else {
+        nhalo = 0;
+    }
+    tr.mark("rows(dev): halo discovery");
+    alloc_vectors();
+    if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
+    if (nnz > 0) {
+        rows_localize_kernel<<<gnz, B, 0, stream>>>(d_colidx.as<int32_t>(), nnz, lo, hi, nloc_pad, d_pos.as<int32_t>());
+        ++launches;
+    }
+    csr = CsrHost();
+    csr.dtype = dtype;
+    csr.rows = nloc;
+    csr.cols = ext_len;
+    stats = RowStats();
+    stats.rows = nloc;
+    stats.nnz = nnz;
+    if (nnz > 0 && nloc > 0) {
+        int* f = d_flags.as<int>();  // [1] max, [2] min, [4..5] padded (u64), [6..7] var (double)
+        const int init_min = INT32_MAX;
+        EIGSOL_CUDA(cudaMemcpyAsync(f + 2, &init_min, sizeof(int), cudaMemcpyHostToDevice, stream));
+        stats.mean = double(nnz) / double(nloc);
+        const unsigned gsl = unsigned(((nloc + 63) / 64 + B - 1) / B);
+        row_stats_kernel<<<gsl, B, 0, stream>>>(d_rowptr.as<int32_t>(), nloc, stats.mean, f + 1, f + 2,
+                                                reinterpret_cast<unsigned long long*>(f + 4), reinterpret_cast<double*>(f + 6));
+        ++launches;
+        int hf[8];
+        EIGSOL_CUDA(cudaMemcpyAsync(hf, f, sizeof hf, cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        unsigned long long padded;
+        double var;
+        std::memcpy(&padded, hf + 4, sizeof padded);
+        std::memcpy(&var, hf + 6, sizeof var);
+        stats.max = hf[1];
+        stats.min = hf[2];
+        stats.cv = stats.mean > 0 ? std::sqrt(var / double(nloc)) / stats.mean : 0.0;
+        stats.sell_fill = double(padded) / double(nnz);
+    }
+    EIGSOL_CUDA(cudaGetLastError());
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    tr.mark("rows(dev): localize + stats");
+    plan_exchange();
+    setup_peer();
+    tr.mark("rows(dev): exchange plan + peer map");
+    if (nranks > 1) {
+        const std::vector<int64_t> all = comm_allgather_i64(comm, local_nnz);
+        nnz_global = 0;
+        for (int64_t v : all) nnz_global += v;
+    } else {
+        nnz_global = local_nnz;
+    }
+    const int forced = env_int("EIGSOL_B200_KERNEL", 0);
+    if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
+    else set_kernel(K_AUTO, 0);
+    tr.mark("rows(dev): kernel choice + unit map");
+}
+
 // Derived layouts (SELL, row blocks, deferred maps) are built on the host from the CSR; after a device-side
 // ingest the host has none yet.
 void MatrixImpl::ensure_host_csr() {
@@ -818,39 +946,34 @@ void MatrixImpl::configure_launch() {
 void MatrixImpl::build_deferred() {
     have_deferred = false;
     unit_start = 0;
-    if (dense || xmode != MODE_PEER || nhalo == 0 || csr.rowptr.empty()) return;
+    if (dense || xmode != MODE_PEER || nhalo == 0 || nloc == 0) return;
     if (!env_int("EIGSOL_B200_DEFER", 1)) return;  // 0: every CTA waits for the halo before its first row
     int64_t nunits = 0;
-    auto unit_of_row = [&](int64_t r) -> int64_t { return r; };
-    (void)unit_of_row;
-    std::vector<int64_t> unit_first;  // first row of each unit (+ end)
+    int rows_per_unit = 0;
+    const int32_t* blk = nullptr;
     switch (kernel) {
         case K_CSR_WINDOW:
-        case K_CSR_SCALAR: nunits = (nloc + block - 1) / block; break;
-        case K_CSR_VECTOR: nunits = (nloc + (block / lanes) - 1) / (block / lanes); break;
-        case K_CSR_STREAM: nunits = nblk; break;
-        case K_SELL: nunits = sell_nslices; break;
+        case K_CSR_SCALAR: rows_per_unit = block; break;
+        case K_CSR_VECTOR: rows_per_unit = block / lanes; break;
+        case K_CSR_STREAM: blk = d_rowblk.as<int32_t>(); nunits = nblk; break;
+        case K_SELL: rows_per_unit = 32 * sell_R; break;
         default: return;
     }
-    std::vector<uint8_t> def(size_t(std::max<int64_t>(nunits, 1)), 0);
-    auto row_reads_halo = [&](int64_t r) {
-        for (int32_t p = csr.rowptr[size_t(r)]; p < csr.rowptr[size_t(r) + 1]; ++p)
-            if (csr.colidx[size_t(p)] >= nloc_pad) return true;
-        return false;
-    };
-    for (int64_t u = 0; u < nunits; ++u) {
-        int64_t r0, r1;
-        switch (kernel) {
-            case K_CSR_WINDOW:
-            case K_CSR_SCALAR: r0 = u * block; r1 = r0 + block; break;
-            case K_CSR_VECTOR: r0 = u * (block / lanes); r1 = r0 + block / lanes; break;
-            case K_CSR_STREAM: r0 = rowblk_h[size_t(u)]; r1 = rowblk_h[size_t(u) + 1]; break;
-            default: r0 = u * 32 * sell_R; r1 = r0 + 32 * sell_R; break;
-        }
-        r1 = std::min<int64_t>(r1, nloc);
-        for (int64_t r = r0; r < r1 && !def[size_t(u)]; ++r)
-            if (row_reads_halo(r)) def[size_t(u)] = 1;
+    if (!blk) nunits = (nloc + rows_per_unit - 1) / rows_per_unit;
+    if (nunits <= 0) return;
+    // computed on the device from the resident (localized) CSR arrays, one warp per unit
+    d_deferred.alloc(size_t(nunits));
+    {
+        const int B = 256;
+        const unsigned g = unsigned((nunits * 32 + B - 1) / B);
+        deferred_units_kernel<<<g, B, 0, stream>>>(d_rowptr.as<int32_t>(), d_colidx.as<int32_t>(), nloc, nunits, rows_per_unit, blk,
+                                                  int32_t(nloc_pad), d_deferred.as<uint8_t>());
+        ++launches;
+        EIGSOL_CUDA(cudaGetLastError());
     }
+    std::vector<uint8_t> def(size_t(nunits), 0);
+    EIGSOL_CUDA(cudaMemcpyAsync(def.data(), d_deferred.p, size_t(nunits), cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
     // longest circular run of units that read no halo entry; the walk starts in its middle
     {
         int64_t best_len = 0, best_begin = 0, run = 0;
@@ -868,9 +991,6 @@ void MatrixImpl::build_deferred() {
         }
         unit_start = nunits > 0 ? int((best_begin + best_len / 2) % nunits) : 0;
     }
-    d_deferred.alloc(def.size());
-    d_deferred.upload(def.data(), def.size(), stream);
-    EIGSOL_CUDA(cudaStreamSynchronize(stream));
     have_deferred = true;
 }
 
@@ -1365,6 +1485,11 @@ int eigsol_b200_matrix_create_csr_rows(int dtype, int64_t n, int64_t row_begin, 
                 if (m.row_begin[r] > m.row_begin[r + 1]) throw PlanError("row blocks of the ranks are not ascending");
             if (m.row_begin[0] != 0 || m.row_begin[m.rank + 1] - m.row_begin[m.rank] != row_count)
                 throw PlanError("row blocks of the ranks do not tile [0, n)");
+        }
+        if (env_int("EIGSOL_B200_DEVICE_INGEST", 1)) {
+            m.init_sparse_device_rows(rowptr, colidx, values);
+            *out = h.release();
+            return int(EIGSOL_B200_OK);
         }
         CsrHost loc;
         loc.dtype = dtype;

@@ -174,4 +174,62 @@ __global__ void row_stats_kernel(const int32_t* __restrict__ rowptr, int64_t row
     atomicAdd(var, v);
 }
 
+// ---- row-block ingest (multi-GPU: each rank holds rows [lo, hi) in CSR with GLOBAL columns) ----------
+// mark[c] = 1 for every referenced column outside [lo, hi); bit 1 of flags = column out of range
+__global__ void rows_mark_kernel(const int32_t* __restrict__ colidx, int64_t nnz, int64_t n, int64_t lo, int64_t hi,
+                                 int32_t* __restrict__ mark, int* flags) {
+    const int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (p >= nnz) return;
+    const int32_t c = colidx[p];
+    if (c < 0 || c >= n) {
+        atomicOr(flags, 2);
+        return;
+    }
+    if ((c < lo || c >= hi) && mark[c] == 0) mark[c] = 1;
+}
+
+// pos = exclusive scan of mark: the sorted distinct remote columns, compacted
+__global__ void halo_compact_kernel(const int32_t* __restrict__ mark, const int32_t* __restrict__ pos, int64_t n,
+                                    int32_t* __restrict__ halo_cols) {
+    const int64_t c = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (c < n && mark[c]) halo_cols[pos[c]] = int32_t(c);
+}
+
+// global column -> extended local numbering [own rows | pad | halo]
+__global__ void rows_localize_kernel(int32_t* __restrict__ colidx, int64_t nnz, int64_t lo, int64_t hi, int64_t nloc_pad,
+                                     const int32_t* __restrict__ pos) {
+    const int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (p >= nnz) return;
+    const int32_t c = colidx[p];
+    colidx[p] = (c >= lo && c < hi) ? int32_t(c - lo) : int32_t(nloc_pad + pos[c]);
+}
+
+// def[u] = 1 if any row of work unit u has an entry in the halo (column >= nloc_pad).  Units are either
+// `rows_per_unit` consecutive rows, or the row blocks [rowblk[u], rowblk[u+1]) when rowblk != nullptr.
+// One warp per unit.
+__global__ void deferred_units_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t rows,
+                                      int64_t nunits, int rows_per_unit, const int32_t* __restrict__ rowblk,
+                                      int32_t nloc_pad, uint8_t* __restrict__ def) {
+    const int64_t u = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (u >= nunits) return;
+    int64_t r0, r1;
+    if (rowblk) {
+        r0 = rowblk[u];
+        r1 = rowblk[u + 1];
+    } else {
+        r0 = u * rows_per_unit;
+        r1 = r0 + rows_per_unit;
+    }
+    r1 = r1 < rows ? r1 : rows;
+    int any = 0;
+    if (r0 < r1) {
+        const int32_t p0 = rowptr[r0], p1 = rowptr[r1];
+        for (int32_t p = p0 + lane; p < p1; p += 32)
+            if (colidx[p] >= nloc_pad) any = 1;
+    }
+    any = __any_sync(0xffffffffu, any);
+    if (lane == 0) def[u] = any ? 1 : 0;
+}
+
 }  // namespace eigsol_b200
