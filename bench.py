@@ -285,11 +285,13 @@ def main():
     t_build = time.time() - t_build
 
     # ---- device-resident timing: W warm-up trips, then exactly K trips ----
+    # the clock sampler (a subprocess) starts BEFORE the warm-up: anything slow on one rank between the barrier
+    # and the timed launches would be waited for, in-kernel, by every other rank and land in their timers
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     dm.begin(x0, 2**31 - 2, -1.0)
     dm.step(args.warmup)
     barrier()
     launches0 = dm.launch_count()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     ms = dm.step(args.steps)  # CUDA events on the launching stream, stream-synchronised on both sides
     launches = dm.launch_count() - launches0
     barrier()
