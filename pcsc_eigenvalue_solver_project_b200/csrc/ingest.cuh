@@ -110,13 +110,7 @@ struct StagedUploader {
 };
 
 // ---- kernels ----------------------------------------------------------------------------------------
-// flags: bit 0 = outer not monotone / outer[0] != 0, bit 1 = row index out of range
-__global__ void csc_check_outer_kernel(const int32_t* __restrict__ outer, int64_t cols, int* flags) {
-    const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (j == 0 && outer[0] != 0) atomicOr(flags, 1);
-    if (j < cols && outer[j + 1] < outer[j]) atomicOr(flags, 1);
-}
-
+// flags: bit 1 = row index out of range (outer is validated on the host: it sizes the allocations)
 // One thread per entry: its column (upper_bound in outer), iota, range check and the row histogram.
 __global__ void csc_expand_kernel(const int32_t* __restrict__ outer, const int32_t* __restrict__ inner, int64_t cols,
                                   int64_t rows, int64_t nnz, int32_t* __restrict__ col, int32_t* __restrict__ iota,

@@ -306,15 +306,6 @@ __device__ __forceinline__ double ld_volatile_f64(const double* p) {
     return v;
 }
 
-__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
 // Spins (one thread, acquire loads: measured cheaper than relaxed loads + a system fence) until the flags of
 // the peers in `mask` have reached `want`; false on timeout.
 __device__ __forceinline__ bool wait_peer_flags(const PeerArgs& pa, unsigned mask, unsigned long long want) {
