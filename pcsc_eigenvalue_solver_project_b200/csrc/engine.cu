@@ -171,6 +171,7 @@ struct MatrixImpl {
     // launch configuration
     int kernel = K_CSR_SCALAR, lanes = 0, grid = 1, block = 256, nslots = 1;
     int64_t stored_bytes = 0;
+    double sigma0 = 1.0;   // power of two near 1/max|a_ij|: scale of the first two launches of a solve
     int64_t launches = 0;  // kernel launches issued over the handle's life
     int issued = 0;        // matvec launches issued since begin (ring phase on the host)
     unsigned long long flag_epoch = 0;  // MODE_PEER: flag base of the current solve (identical on every rank)
@@ -192,6 +193,7 @@ struct MatrixImpl {
     void init_sparse_local(CsrHost&& local_global_cols);
     void init_sparse_device_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner, const void* values);
     void ensure_host_csr();
+    void compute_prescale();
     void init_sparse_device_rows(const int32_t* rowptr, const int32_t* colidx, const void* values);
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
     void plan_exchange();
@@ -215,7 +217,7 @@ struct MatrixImpl {
     void configure_launch();
     void drop_graph();
 
-    void begin(const void* x0, int max_it, double tol);
+    void begin(const void* x0, int max_it, double tol, bool unit_scale = false);
     void exchange_halo(int in);
     void launch_matvec(int phase);
     void build_deferred();
@@ -469,6 +471,7 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     const KernelChoice ch = choose_kernel(dtype, stats);
     if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
     else set_kernel(ch.kernel, ch.lanes);
+    compute_prescale();
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -578,6 +581,7 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
     const int forced = env_int("EIGSOL_B200_KERNEL", 0);
     if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
     else set_kernel(K_AUTO, 0);
+    compute_prescale();
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -704,6 +708,7 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     const int forced = env_int("EIGSOL_B200_KERNEL", 0);
     if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
     else set_kernel(K_AUTO, 0);
+    compute_prescale();
     tr.mark("rows(dev): kernel choice + unit map");
 }
 
@@ -721,6 +726,31 @@ void MatrixImpl::ensure_host_csr() {
         EIGSOL_CUDA(cudaMemcpyAsync(csr.vals.data(), d_vals.p, size_t(local_nnz) * size_t(ss()), cudaMemcpyDeviceToHost, stream));
     }
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
+}
+
+// sigma0 from max |a_ij| over the resident matrix values (all ranks agree on the global maximum).
+void MatrixImpl::compute_prescale() {
+    sigma0 = 1.0;
+    const double* vals = dense ? d_dense.as<double>() : d_vals.as<double>();
+    const int64_t count = (dense ? lda * ext_len : local_nnz) * (dtype ? 2 : 1);
+    DevBuf d_max;
+    d_max.alloc(sizeof(unsigned long long));
+    if (count > 0) {
+        const int g = int(std::max<int64_t>(1, std::min<int64_t>((count + 255) / 256, int64_t(sm_count) * 8)));
+        absmax_kernel<<<g, 256, 0, stream>>>(vals, count, d_max.as<unsigned long long>());
+        ++launches;
+        EIGSOL_CUDA(cudaGetLastError());
+    }
+    unsigned long long bits = 0;
+    EIGSOL_CUDA(cudaMemcpyAsync(&bits, d_max.p, sizeof bits, cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    if (nranks > 1) {
+        const std::vector<int64_t> all = comm_allgather_i64(comm, int64_t(bits));
+        for (int64_t v : all) bits = std::max<unsigned long long>(bits, (unsigned long long)v);
+    }
+    double amax;
+    std::memcpy(&amax, &bits, sizeof amax);
+    sigma0 = prescale_from_amax(amax);
 }
 
 void MatrixImpl::drop_graph() {
@@ -874,6 +904,7 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
     copy_cols(hi, n - hi, nloc_pad + lo);
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
     set_kernel(K_GEMV, 0);
+    compute_prescale();
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -1066,18 +1097,18 @@ void MatrixImpl::launch_matvec(int phase) {
 // -------------------------------------------------------------------------------------------------
 // The loop.
 // -------------------------------------------------------------------------------------------------
-void MatrixImpl::begin(const void* x0, int max_it, double tol) {
+void MatrixImpl::begin(const void* x0, int max_it, double tol, bool unit_scale) {
     if (!x0) throw PlanError("null start vector");
     EIGSOL_CUDA(cudaSetDevice(device));
     PowerState st;
     std::memset(&st, 0, sizeof st);
     st.q[0] = 1.0;  // x0 arrives normalised (power_method.hpp:62); launch 0 uses it as is
-    st.sigma[0] = 1.0;
+    st.sigma[0] = unit_scale ? 1.0 : sigma0;
     st.tol = tol;
     st.final_q = 1.0;
     st.max_trips = max_it;
     st.stop = max_it <= 0 ? STOP_MAX_TRIPS : STOP_NONE;  // the loop of :68 never runs
-    st.ctrl[0].sigma = 1.0;
+    st.ctrl[0].sigma = st.sigma[0];
     st.ctrl[0].launch_no = 0;
     st.ctrl[0].active = max_it > 0 ? 1 : 0;
     max_trips = max_it;
@@ -1292,7 +1323,7 @@ void MatrixImpl::run(const void* x0, int max_it, double tol, void* x_out, double
 
 // y = A x alone: launch 0 of the loop with ||x|| taken as 1 leaves A x un-normalised in buffer 1.
 void MatrixImpl::matvec(const void* x, void* y) {
-    begin(x, 1, -1.0);
+    begin(x, 1, -1.0, true);
     issue_trips(1);
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
     gather_download(buf[1].p, y);
@@ -1303,7 +1334,7 @@ void MatrixImpl::matvec(const void* x, void* y) {
 // method, src/power_method/shifted_inverse_power_solver.hpp:62, `x.dot(A * x)`): launch 0 of the loop with
 // sigma = 1 leaves exactly these sums; the control-only launch folds them into the state.
 void MatrixImpl::rayleigh(const void* x, double out[4]) {
-    begin(x, 1, -1.0);
+    begin(x, 1, -1.0, true);
     issue_trips(1);
     const PowerState st = poll_state();
     out[0] = st.last_a[0];

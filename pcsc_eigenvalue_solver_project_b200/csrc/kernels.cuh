@@ -187,7 +187,7 @@ struct PowerState {
 enum { STOP_NONE = 0, STOP_CONVERGED = 1, STOP_ZERO_NORM = 2, STOP_MAX_TRIPS = 3, STOP_ERROR = 4 };
 
 // tolerance.hpp:28-33 with a = lambdaNew, b = lambda: |a-b| <= tol*(1+|a|), |.| the complex modulus.
-__device__ __forceinline__ bool close_relative(double are, double aim, double bre, double bim, double tol) {
+__host__ __device__ __forceinline__ bool close_relative(double are, double aim, double bre, double bim, double tol) {
     const double diff = hypot(are - bre, aim - bim);
     const double scale = 1.0 + hypot(are, aim);
     return diff <= tol * scale;
@@ -195,7 +195,7 @@ __device__ __forceinline__ bool close_relative(double are, double aim, double br
 
 // Folds the global sums of launch j (a = v_j^H z, qn = ||v_{j+1}||^2) into the state.  For j >= 1 this
 // closes trip k = j-1 of power_method.hpp:68-96: x_{k+1} = v_j / ||v_j|| and lambdaNew = x^H A x.
-__device__ __forceinline__ void fold_launch(PowerState* st, int j, double are, double aim, double qn) {
+__host__ __device__ __forceinline__ void fold_launch(PowerState* st, int j, double are, double aim, double qn) {
     const int r = j % kRing;
     st->q[(j + 1) % kRing] = qn;
     st->last_a[0] = are;
@@ -230,8 +230,18 @@ __device__ __forceinline__ void fold_launch(PowerState* st, int j, double are, d
 
 // Scale of launch m+1, from what is known after folding launch m-1: growth^2 g2 = ||A v||^2/||v||^2 seen
 // in launch m-1 and the predicted ||v_{m+1}||^2 = sigma_m^2 g2 q_m.  Rounded to a power of two.
-__device__ __forceinline__ double next_sigma(const PowerState* st, int m) {
-    if (m == 0) return 1.0;
+// Scale of the first two launches, before any norm has been seen: a power of two near 1/max|a_ij| (found once
+// at upload), so that matrices scaled by 1e+-150 neither overflow nor underflow (which would read as the
+// ||y|| == 0 exit) during the two launches the adaptive scale needs to catch up.
+__host__ __device__ __forceinline__ double prescale_from_amax(double amax) {
+    if (!(amax > 0.0) || !isfinite(amax)) return 1.0;
+    const int k = int(rint(log2(amax)));
+    if (k > 1000 || k < -1000) return 1.0;
+    return ldexp(1.0, -k);
+}
+
+__host__ __device__ __forceinline__ double next_sigma(const PowerState* st, int m) {
+    if (m == 0) return st->sigma[0];
     const int r = m % kRing, p = (m - 1) % kRing;
     const double qm = st->q[r], qp = st->q[p], sm = st->sigma[r], sp = st->sigma[p];
     const double g2 = qm / (sp * sp * qp);
@@ -241,6 +251,43 @@ __device__ __forceinline__ double next_sigma(const PowerState* st, int m) {
     const int k = int(rint(0.5 * log2(x)));
     if (k > 900 || k < -900) return 1.0;
     return ldexp(1.0, -k);
+}
+
+// The control CTA's decisions, separated from how the sums reach it so that tests can drive the same state
+// machine on the host (tests/statemachine/sim.cu).  `control_wants_fold`: launch launch_no-1 ran actively and
+// its sums are not folded yet.  `control_apply`: fold them (or note a no-op launch, or an error), and --
+// in a matvec launch (advance) -- write the control record of launch m+1 and count launch m.
+struct ControlPlan {
+    int m, j;
+    bool have, fold;
+};
+__host__ __device__ __forceinline__ ControlPlan control_wants_fold(const PowerState* st) {
+    ControlPlan p;
+    p.m = st->launch_no;
+    p.j = p.m - 1;
+    p.have = p.j >= 0 && st->folded == p.j;
+    p.fold = p.have && st->ctrl[(p.j + kRing) % kRing].active && st->stop == STOP_NONE && !st->error;
+    return p;
+}
+__host__ __device__ __forceinline__ void control_apply(PowerState* st, const ControlPlan& p, bool ok, double a, double b,
+                                                       double d, bool advance) {
+    if (!ok || *(volatile int*)&st->error) {
+        st->error = 1;
+        st->stop = STOP_ERROR;
+    } else if (p.fold) {
+        fold_launch(st, p.j, a, b, d);
+    } else if (p.have) {
+        st->folded = p.j + 1;  // launch j was a no-op
+    }
+    if (advance) {
+        LaunchCtrl nc;
+        nc.sigma = next_sigma(st, p.m);
+        nc.launch_no = p.m + 1;
+        nc.active = (st->stop == STOP_NONE && p.m + 1 <= st->max_trips) ? 1 : 0;
+        st->sigma[(p.m + 1) % kRing] = nc.sigma;
+        st->ctrl[(p.m + 1) % kRing] = nc;
+        st->launch_no = p.m + 1;
+    }
 }
 
 // How the sums of a launch become global and how the halo of x travels.
@@ -368,11 +415,11 @@ template <class S, int BLOCK>
 __device__ void control_cta(const IterArgs<S>& it, bool advance) {
     __shared__ double sred[3][BLOCK / 32];
     PowerState* st = it.st;
-    const int m = st->launch_no;
-    const int j = m - 1;  // the launch whose sums are folded now
+    const ControlPlan plan = control_wants_fold(st);
+    const int m = plan.m;
+    const int j = plan.j;  // the launch whose sums are folded now
     const unsigned long long flagv = st->flag_base + (unsigned long long)m;
-    const bool have = j >= 0 && st->folded == j;
-    const bool fold = have && st->ctrl[(j + kRing) % kRing].active && st->stop == STOP_NONE && !st->error;
+    const bool fold = plan.fold;
     double a = 0.0, b = 0.0, d = 0.0;
     if (fold) {
         const double* part = it.partials + size_t(j % kRing) * size_t(it.nslots) * 3;
@@ -451,23 +498,7 @@ __device__ void control_cta(const IterArgs<S>& it, bool advance) {
         b = __ldcg(sc + 1);
         d = __ldcg(sc + 2);
     }
-    if (!ok || *(volatile int*)&st->error) {
-        st->error = 1;
-        st->stop = STOP_ERROR;
-    } else if (fold) {
-        fold_launch(st, j, a, b, d);
-    } else if (have) {
-        st->folded = j + 1;  // launch j was a no-op
-    }
-    if (advance) {
-        LaunchCtrl nc;
-        nc.sigma = next_sigma(st, m);
-        nc.launch_no = m + 1;
-        nc.active = (st->stop == STOP_NONE && m + 1 <= st->max_trips) ? 1 : 0;
-        st->sigma[(m + 1) % kRing] = nc.sigma;
-        st->ctrl[(m + 1) % kRing] = nc;
-        st->launch_no = m + 1;
-    }
+    control_apply(st, plan, ok != 0, a, b, d, advance);
 }
 
 // Control-only launch (host poll / end): one CTA.
@@ -1004,6 +1035,21 @@ __global__ void __launch_bounds__(BLOCK) reduce_partials_kernel(const double* pa
         scal[1] = b;
         scal[2] = d;
     }
+}
+
+// max |a| over an array of doubles (complex: over re and im parts), as the bit pattern of a non-negative double
+__global__ void absmax_kernel(const double* __restrict__ a, int64_t count, unsigned long long* out) {
+    double m = 0.0;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += int64_t(gridDim.x) * blockDim.x) {
+        const double v = fabs(a[i]);
+        m = v > m ? v : m;  // NaNs are skipped
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        const double o = __shfl_down_sync(0xffffffffu, m, d);
+        m = o > m ? o : m;
+    }
+    if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));
 }
 
 // x = y / normY (power_method.hpp:78, true division) of the result buffer -> contiguous output.

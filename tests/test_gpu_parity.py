@@ -410,3 +410,20 @@ def test_full_size_config3_against_oracle(orc):
     x0 = es.random_unit(8192, np.float64, seed=1)
     r = es.powerMethod(es.Matrix(a), es.SolverOptions(3, -1.0), x0=x0)
     check_result(r, orc.power_dense(a, x0, 3, -1.0))
+
+
+@pytest.mark.parametrize("scale", [1e150, 1e-150])
+def test_extreme_matrix_scales(orc, scale):
+    """Matrices scaled by 1e+-150: the stored vector is rescaled by powers of two (first from max|a_ij|, then from
+    the norms seen), so nothing overflows and a tiny ||y|| is not mistaken for the ||y|| == 0 exit."""
+    g = 24
+    n = g * g
+    rowptr, colidx, vals = gen.laplacian_2d(g)
+    outer, inner, cv = csc_of(rowptr, colidx, vals * scale)
+    x0 = orc.random_unit(n, np.float64, seed=3)
+    r = es.powerMethod(es.Matrix(((n, n), outer, inner, cv)), es.SolverOptions(60, -1.0), x0=x0)
+    check_result(r, orc.power_csc((n, n), outer, inner, cv, x0, 60, -1.0))
+    a = gen.dense_random_symmetric(48, seed=9) * scale
+    x0 = orc.random_unit(48, np.float64, seed=4)
+    r = es.powerMethod(es.Matrix(a), es.SolverOptions(40, -1.0), x0=x0)
+    check_result(r, orc.power_dense(a, x0, 40, -1.0))
