@@ -53,7 +53,8 @@ typedef enum eigsol_b200_status {
     EIGSOL_B200_ERR_NOT_SQUARE = 2, /* power_method.hpp:52-55  "powerMethod: matrix must be square"  */
     EIGSOL_B200_ERR_ZERO_SIZE = 3,  /* power_method.hpp:56-58  "powerMethod: matrix has zero size"   */
     EIGSOL_B200_ERR_DEVICE = 4,     /* CUDA / NCCL failure, or no device: "powerMethod: device error: ..." */
-    EIGSOL_B200_ERR_STATE = 5       /* call sequence error on a handle (step before begin, ...)          */
+    EIGSOL_B200_ERR_STATE = 5,      /* call sequence error on a handle (step before begin, ...)          */
+    EIGSOL_B200_ERR_IO = 6          /* matrix file cannot be opened / is malformed: the reader's messages  */
 } eigsol_b200_status;
 
 enum { EIGSOL_B200_F64 = 0, EIGSOL_B200_C128 = 1 };
@@ -204,6 +205,35 @@ EIGSOL_B200_API int eigsol_b200_comm_create(int rank, int nranks, const void* id
 EIGSOL_B200_API int eigsol_b200_comm_destroy(eigsol_b200_comm* comm);
 /* Device-side barrier + max over ranks of a float (bench timing: max over ranks of event times). */
 EIGSOL_B200_API int eigsol_b200_comm_max_float(eigsol_b200_comm* comm, float* inout);
+
+/* ---- matrix files: the reference's text format read fast, and a mappable binary container (no GPU needed) ----
+ *
+ * eigsol_b200_read_matrix_text replaces EigSol::readMatrixFromFile<Scalar>(filename)
+ * (src/reader/file_matrix_reader.hpp:170-200; dense branch :33-66, sparse branch :84-132; format README.md:87-171):
+ * the file is mapped and parsed by all host threads; `dtype` is the Scalar it is read as (two reals per value
+ * for EIGSOL_B200_C128).  On return the struct holds exactly what the reference's Matrix would own: dense ->
+ * values[rows*cols] column-major (Matrix::Dense<Scalar>); sparse -> outer[cols+1], inner[nnz], values[nnz], rows
+ * ascending inside a column (a compressed Matrix::Sparse<Scalar>).  Failures return EIGSOL_B200_ERR_IO with the
+ * reference's message ("Impossible to open the file: ...", "Unknown storage type: ...", "Sparse indices out of
+ * range", ...).  The arrays belong to the struct until eigsol_b200_file_matrix_release.
+ * The binary container (EIGSOLB2: 64-byte header + 64-byte aligned arrays) is mapped, not parsed: its pointers
+ * can go straight into eigsol_b200_matrix_create_csc / _dense. */
+typedef struct eigsol_b200_file_matrix {
+    int32_t dtype;
+    int32_t is_dense;
+    int64_t rows, cols, nnz;   /* nnz: stored entries (dense: rows*cols) */
+    const int32_t* outer;      /* sparse only */
+    const int32_t* inner;      /* sparse only */
+    const void* values;
+    void* owner;               /* internal */
+} eigsol_b200_file_matrix;
+
+EIGSOL_B200_API int eigsol_b200_read_matrix_text(const char* path, int dtype, eigsol_b200_file_matrix* out);
+EIGSOL_B200_API int eigsol_b200_read_matrix_bin(const char* path, eigsol_b200_file_matrix* out);
+EIGSOL_B200_API int eigsol_b200_write_matrix_bin(const char* path, int dtype, int is_dense, int64_t rows,
+                                                 int64_t cols, int64_t nnz, const int32_t* outer,
+                                                 const int32_t* inner, const void* values);
+EIGSOL_B200_API int eigsol_b200_file_matrix_release(eigsol_b200_file_matrix* m);
 
 /* ---- host-side planning, no GPU needed (unit-testable on CPU; used internally at upload) ------- */
 

@@ -23,6 +23,7 @@
 #include "src/matrix/matrix.hpp"
 #include "src/option/solver_option.hpp"
 #include "src/power_method/power_method.hpp"
+#include "src/reader/file_matrix_reader.hpp"  // EigSol::readMatrixFromFile (:170-200), included once: it has no include guard
 
 #define REF_API extern "C" __attribute__((visibility("default")))
 
@@ -175,3 +176,43 @@ REF_API int ref_is_close_relative(int dtype, const double a[2], const double b[2
 }
 
 REF_API void ref_srand(unsigned seed) { std::srand(seed); }
+
+// ---- the reference's file reader (src/reader/file_matrix_reader.hpp:170-200), for pinning the fast reader ----
+// Reads `path` as Scalar = double (dtype 0) or complex<double> (1) and copies out what the returned Matrix owns.
+// Call once with null arrays to get the sizes.  Returns 0, or 1 with the reference's exception text in
+// ref_last_error().  seconds_out = time spent inside readMatrixFromFile.
+REF_API int ref_read_matrix_file(const char* path, int dtype, int* is_dense, int64_t* rows, int64_t* cols, int64_t* nnz,
+                                 int32_t* outer, int32_t* inner, void* values, double* seconds_out) {
+    try {
+        const auto t0 = std::chrono::steady_clock::now();
+        auto copy_out = [&](auto tag) {
+            using S = decltype(tag);
+            // Matrix is neither copyable nor movable: read in place and copy the arrays out
+            const EigSol::Matrix mat = EigSol::readMatrixFromFile<S>(std::string(path));
+            const auto t1 = std::chrono::steady_clock::now();
+            if (seconds_out) *seconds_out = std::chrono::duration<double>(t1 - t0).count();
+            *is_dense = mat.isDense() ? 1 : 0;
+            if (mat.isDense()) {
+                const auto& d = mat.cast<EigSol::Matrix::Dense<S>>();
+                *rows = d.rows();
+                *cols = d.cols();
+                *nnz = int64_t(d.rows()) * d.cols();
+                if (values) std::memcpy(values, d.data(), sizeof(S) * size_t(*nnz));
+            } else {
+                const auto& sp = mat.cast<EigSol::Matrix::Sparse<S>>();
+                *rows = sp.rows();
+                *cols = sp.cols();
+                *nnz = sp.nonZeros();
+                if (outer) std::memcpy(outer, sp.outerIndexPtr(), sizeof(int32_t) * size_t(sp.cols() + 1));
+                if (inner) std::memcpy(inner, sp.innerIndexPtr(), sizeof(int32_t) * size_t(*nnz));
+                if (values) std::memcpy(values, sp.valuePtr(), sizeof(S) * size_t(*nnz));
+            }
+        };
+        if (dtype) copy_out(cd{});
+        else copy_out(double{});
+        return 0;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}

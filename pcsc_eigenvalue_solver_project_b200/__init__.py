@@ -18,6 +18,8 @@ from __future__ import annotations
 import ctypes as C
 from dataclasses import dataclass, field
 
+import os
+
 import numpy as np
 
 from . import _capi
@@ -25,7 +27,8 @@ from ._capi import (C128, F64, KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_STREAM
                     KERNEL_NAMES, KERNEL_SELL, EigsolB200Error)
 
 __all__ = ["Matrix", "SolverOptions", "EigenResult", "powerMethod", "power_method", "DeviceMatrix", "Comm",
-           "random_unit", "srand", "device_count", "EigsolB200Error"]
+           "random_unit", "srand", "device_count", "EigsolB200Error", "readMatrixFromFile",
+           "writeMatrixBinary", "readMatrixBinary"]
 
 
 # --------------------------------------------------------------------------------------------------
@@ -191,6 +194,61 @@ power_method = powerMethod
 # --------------------------------------------------------------------------------------------------
 # Handle API: device-resident matrix (upload once, iterate many) and multi-GPU ranks.
 # --------------------------------------------------------------------------------------------------
+def _matrix_from_file_struct(fm) -> "Matrix":
+    """Copies the arrays of an eigsol_b200_file_matrix into a Matrix (which stores by value, matrix.hpp:187-204)."""
+    dt = np.complex128 if fm.dtype else np.float64
+    rows, cols, nnz = int(fm.rows), int(fm.cols), int(fm.nnz)
+    vals = np.ctypeslib.as_array(C.cast(fm.values, C.POINTER(C.c_double)), shape=(nnz * (2 if fm.dtype else 1),))
+    vals = vals.view(dt) if fm.dtype else vals
+    if fm.is_dense:
+        return Matrix(np.array(vals.reshape((cols, rows)).T, order="F", copy=True))
+    outer = np.ctypeslib.as_array(fm.outer, shape=(cols + 1,)).copy()
+    inner = np.ctypeslib.as_array(fm.inner, shape=(max(nnz, 1),))[:nnz].copy()
+    return Matrix(((rows, cols), outer, inner, vals.copy()))
+
+
+def readMatrixFromFile(filename: str, dtype=np.float64) -> "Matrix":
+    """``EigSol::readMatrixFromFile<Scalar>(filename)`` (src/reader/file_matrix_reader.hpp:170-200): the reference's
+    text format (README.md:87-171) parsed by all host threads.  ``dtype`` plays the template argument: complex
+    reads two reals per value.  Raises ``RuntimeError`` with the reference's messages."""
+    fm = _capi.FileMatrix()
+    st = _capi.lib().eigsol_b200_read_matrix_text(os.fsencode(filename), _capi.dtype_code(np.dtype(dtype)), C.byref(fm))
+    if st == _capi.ERR_IO:
+        raise RuntimeError(_capi.last_error())
+    _capi.check(st)
+    try:
+        return _matrix_from_file_struct(fm)
+    finally:
+        _capi.lib().eigsol_b200_file_matrix_release(C.byref(fm))
+
+
+def writeMatrixBinary(m: "Matrix", filename: str) -> None:
+    """Stores a Matrix in the mappable EIGSOLB2 container (64-byte header + 64-byte aligned raw arrays)."""
+    L = _capi.lib()
+    code = _capi.dtype_code(m._dtype)
+    if m.isDense():
+        a = m._a
+        _capi.check(L.eigsol_b200_write_matrix_bin(os.fsencode(filename), code, 1, a.shape[0], a.shape[1], a.size,
+                                                    None, None, _capi.ptr(a)))
+    else:
+        _capi.check(L.eigsol_b200_write_matrix_bin(os.fsencode(filename), code, 0, m._shape[0], m._shape[1],
+                                                    int(m._outer[-1]), _capi.ptr(m._outer), _capi.ptr(m._inner),
+                                                    _capi.ptr(m._values)))
+
+
+def readMatrixBinary(filename: str) -> "Matrix":
+    """Maps an EIGSOLB2 container (no parsing) and wraps its arrays in a Matrix."""
+    fm = _capi.FileMatrix()
+    st = _capi.lib().eigsol_b200_read_matrix_bin(os.fsencode(filename), C.byref(fm))
+    if st == _capi.ERR_IO:
+        raise RuntimeError(_capi.last_error())
+    _capi.check(st)
+    try:
+        return _matrix_from_file_struct(fm)
+    finally:
+        _capi.lib().eigsol_b200_file_matrix_release(C.byref(fm))
+
+
 class Comm:
     """One rank of a multi-GPU group (one process per GPU).  ``unique_id()`` on rank 0, broadcast the
     128 bytes with whatever the host program has (torch.distributed, MPI, a file), then construct."""

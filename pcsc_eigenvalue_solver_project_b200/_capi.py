@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libeigsol_b200.so")
 
-OK, ERR_INVALID, ERR_NOT_SQUARE, ERR_ZERO_SIZE, ERR_DEVICE, ERR_STATE = range(6)
+OK, ERR_INVALID, ERR_NOT_SQUARE, ERR_ZERO_SIZE, ERR_DEVICE, ERR_STATE, ERR_IO = range(7)
 F64, C128 = 0, 1
 KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_VECTOR, KERNEL_CSR_STREAM, KERNEL_SELL, KERNEL_GEMV, KERNEL_CSR_WINDOW = range(7)
 KERNEL_NAMES = {0: "auto", 1: "csr_scalar", 2: "csr_vector", 3: "csr_stream", 4: "sell", 5: "gemv", 6: "csr_window"}
@@ -27,11 +27,21 @@ EXPORTS = [
     "eigsol_b200_matrix_destroy", "eigsol_b200_matrix_get_info", "eigsol_b200_matrix_set_kernel",
     "eigsol_b200_power_run", "eigsol_b200_power_begin", "eigsol_b200_power_step", "eigsol_b200_power_end",
     "eigsol_b200_matvec", "eigsol_b200_rayleigh", "eigsol_b200_matrix_launch_count",
+    "eigsol_b200_read_matrix_text", "eigsol_b200_read_matrix_bin", "eigsol_b200_write_matrix_bin",
+    "eigsol_b200_file_matrix_release",
     "eigsol_b200_comm_unique_id", "eigsol_b200_comm_create", "eigsol_b200_comm_destroy",
     "eigsol_b200_comm_max_float",
     "eigsol_b200_csc_to_csr", "eigsol_b200_partition_rows", "eigsol_b200_halo_plan",
     "eigsol_b200_choose_kernel", "eigsol_b200_random_unit",
 ]
+
+
+class FileMatrix(C.Structure):
+    """eigsol_b200_file_matrix (include/eigsol_b200.h)."""
+    _fields_ = [
+        ("dtype", C.c_int32), ("is_dense", C.c_int32), ("rows", C.c_int64), ("cols", C.c_int64), ("nnz", C.c_int64),
+        ("outer", C.POINTER(C.c_int32)), ("inner", C.POINTER(C.c_int32)), ("values", C.c_void_p), ("owner", C.c_void_p),
+    ]
 
 
 class MatrixInfo(C.Structure):
@@ -92,6 +102,10 @@ def lib():
         "eigsol_b200_matvec": (i, [vp, vp, vp]),
         "eigsol_b200_rayleigh": (i, [vp, vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "eigsol_b200_matrix_launch_count": (i64, [vp]),
+        "eigsol_b200_read_matrix_text": (i, [C.c_char_p, i, C.POINTER(FileMatrix)]),
+        "eigsol_b200_read_matrix_bin": (i, [C.c_char_p, C.POINTER(FileMatrix)]),
+        "eigsol_b200_write_matrix_bin": (i, [C.c_char_p, i, i, i64, i64, i64, vp, vp, vp]),
+        "eigsol_b200_file_matrix_release": (i, [C.POINTER(FileMatrix)]),
         "eigsol_b200_comm_unique_id": (i, [vp]),
         "eigsol_b200_comm_create": (i, [i, i, vp, i, C.POINTER(vp)]),
         "eigsol_b200_comm_destroy": (i, [vp]),

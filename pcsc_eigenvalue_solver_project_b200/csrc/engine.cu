@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "../../include/eigsol_b200.h"
+#include "fileio.hpp"
 #include "ingest.cuh"
 #include "kernels.cuh"
 #include "plan.hpp"
@@ -1403,6 +1404,9 @@ template <class F> int guarded(F&& f) {
     } catch (const StateError& e) {
         g_last_error = e.what();
         return EIGSOL_B200_ERR_STATE;
+    } catch (const IoError& e) {
+        g_last_error = e.what();
+        return EIGSOL_B200_ERR_IO;
     } catch (const PlanError& e) {
         g_last_error = std::string("eigsol_b200: invalid argument: ") + e.what();
         return EIGSOL_B200_ERR_INVALID;
@@ -1735,6 +1739,74 @@ int eigsol_b200_comm_max_float(eigsol_b200_comm* comm, float* inout) {
         EIGSOL_CUDA(cudaStreamSynchronize(c.stream));
         return int(EIGSOL_B200_OK);
     });
+}
+
+// ---- matrix files (no GPU) ----------------------------------------------------------------------------
+namespace {
+struct FileOwner {
+    std::unique_ptr<FileMatrixHost> parsed;
+    std::unique_ptr<MappedMatrix> mapped;
+};
+}  // namespace
+
+int eigsol_b200_read_matrix_text(const char* path, int dtype, eigsol_b200_file_matrix* out) {
+    if (!path || !out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    std::memset(out, 0, sizeof *out);
+    if (int e = check_dtype(dtype)) return e;
+    return guarded([&] {
+        std::unique_ptr<FileOwner> o(new FileOwner);
+        o->parsed.reset(new FileMatrixHost(read_matrix_text(path, dtype)));
+        const FileMatrixHost& m = *o->parsed;
+        out->dtype = m.dtype;
+        out->is_dense = m.dense ? 1 : 0;
+        out->rows = m.rows;
+        out->cols = m.cols;
+        out->nnz = m.dense ? m.rows * m.cols : m.nnz;
+        out->outer = m.dense ? nullptr : m.outer.data();
+        out->inner = m.dense ? nullptr : m.inner.data();
+        out->values = m.values.data();
+        out->owner = o.release();
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_read_matrix_bin(const char* path, eigsol_b200_file_matrix* out) {
+    if (!path || !out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    std::memset(out, 0, sizeof *out);
+    return guarded([&] {
+        std::unique_ptr<FileOwner> o(new FileOwner);
+        o->mapped.reset(new MappedMatrix(path));
+        const MappedMatrix& m = *o->mapped;
+        out->dtype = m.h.dtype;
+        out->is_dense = m.h.dense;
+        out->rows = m.h.rows;
+        out->cols = m.h.cols;
+        out->nnz = m.h.nnz;
+        out->outer = m.outer;
+        out->inner = m.inner;
+        out->values = m.values;
+        out->owner = o.release();
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_write_matrix_bin(const char* path, int dtype, int is_dense, int64_t rows, int64_t cols, int64_t nnz,
+                                 const int32_t* outer, const int32_t* inner, const void* values) {
+    if (!path || !values || (!is_dense && (!outer || !inner)))
+        return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    if (int e = check_dtype(dtype)) return e;
+    if (rows <= 0 || cols <= 0 || nnz < 0) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: bad dimensions");
+    return guarded([&] {
+        write_matrix_bin(path, dtype, is_dense != 0, rows, cols, nnz, outer, inner, values);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_file_matrix_release(eigsol_b200_file_matrix* m) {
+    if (!m) return EIGSOL_B200_OK;
+    delete static_cast<FileOwner*>(m->owner);
+    std::memset(m, 0, sizeof *m);
+    return EIGSOL_B200_OK;
 }
 
 // ---- host-side planning (no GPU) ------------------------------------------------------------------

@@ -121,6 +121,9 @@ class Reference:
         L.ref_matvec.argtypes = [_vp, _vp, _vp]
         L.ref_is_close_relative.restype = _i
         L.ref_is_close_relative.argtypes = [_i, _vp, _vp, _d]
+        if hasattr(L, "ref_read_matrix_file"):
+            L.ref_read_matrix_file.restype = _i
+            L.ref_read_matrix_file.argtypes = [C.c_char_p, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
         self.L = L
 
     def last_error(self):
@@ -156,6 +159,22 @@ class Reference:
         st = self.L.ref_matvec(h, _p(x), _p(y))
         assert st == 0, self.last_error()
         return y
+
+    def read_matrix_file(self, path, dtype):
+        """EigSol::readMatrixFromFile<Scalar>(path) of the compiled reference: returns
+        (is_dense, rows, cols, outer, inner, values, seconds) or raises RuntimeError with its message."""
+        cplx = is_complex(dtype)
+        isd, rows, cols, nnz, sec = C.c_int(0), C.c_int64(0), C.c_int64(0), C.c_int64(0), C.c_double(0.0)
+        args = (os.fsencode(path), cplx, C.byref(isd), C.byref(rows), C.byref(cols), C.byref(nnz))
+        if self.L.ref_read_matrix_file(*args, None, None, None, C.byref(sec)) != 0:
+            raise RuntimeError(self.last_error())
+        vals = np.empty(max(nnz.value, 1), dtype=np.complex128 if cplx else np.float64)
+        outer = np.empty(cols.value + 1, dtype=np.int32)
+        inner = np.empty(max(nnz.value, 1), dtype=np.int32)
+        if self.L.ref_read_matrix_file(*args, _p(outer), _p(inner), _p(vals), None) != 0:
+            raise RuntimeError(self.last_error())
+        n = nnz.value
+        return bool(isd.value), rows.value, cols.value, outer, inner[:n], vals[:n], sec.value
 
     def is_close_relative(self, dtype, a, b, tol):
         aa = np.array([complex(a).real, complex(a).imag])
