@@ -1,0 +1,377 @@
+// blockmath.hpp -- the k x k dense algebra and the control step of the BLOCK power iteration.
+//
+// Block (simultaneous) power iteration keeps k vectors instead of the one of power_method.hpp:68-96:
+//     Q_m = orth(U_m)            U_{m+1} = A Q_m            H_m = Q_m^H A Q_m  (k x k)
+// and reads the k dominant eigenvalues off H_m (Rayleigh-Ritz).  With k = 1 this IS the reference's loop:
+// Q = x / ||x||, H = x^H A x (power_method.hpp:78,81), same convergence test (:83-91, tolerance.hpp:28-33) on
+// every wanted Ritz value, same `initialized` / usedIters bookkeeping.  The n-sized work (A Q, the Gram
+// sums) is one pass of the SpMM kernel in block.cuh; everything here is k x k, k <= 8, and runs in ONE
+// thread of the control kernel between two launches -- and, compiled by g++, in tests/blockmath on the CPU.
+//
+//   orth by Cholesky QR:   W = U^H U = R^H R  ->  Q = U T,  T = R^{-1}      (chol_upper, tri_inverse_upper)
+//   Ritz pairs:            H = Z Tm Z^H (complex Schur: Givens Hessenberg reduction + shifted QR), then the
+//                          eigenvectors of the triangular factor by back substitution   (eig_general)
+// All arithmetic is complex double; a real matrix simply has conjugate-pair Ritz values.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define EB_HD __host__ __device__ __forceinline__
+#define EB_HDN __host__ __device__ __noinline__
+#else
+#define EB_HD inline
+#define EB_HDN inline
+#endif
+
+namespace eigsol_b200 {
+
+constexpr int kBlockMax = 8;               // largest block width
+constexpr int kBlockLd = kBlockMax;        // row stride of every k x k array below
+constexpr int kBlockElems = kBlockMax * kBlockMax;
+
+struct Cx {
+    double re, im;
+};
+EB_HD Cx cx(double re, double im = 0.0) {
+    Cx r;
+    r.re = re;
+    r.im = im;
+    return r;
+}
+EB_HD Cx operator+(Cx a, Cx b) { return cx(a.re + b.re, a.im + b.im); }
+EB_HD Cx operator-(Cx a, Cx b) { return cx(a.re - b.re, a.im - b.im); }
+EB_HD Cx operator-(Cx a) { return cx(-a.re, -a.im); }
+EB_HD Cx operator*(Cx a, Cx b) { return cx(a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re); }
+EB_HD Cx operator*(double s, Cx a) { return cx(s * a.re, s * a.im); }
+EB_HD Cx conj(Cx a) { return cx(a.re, -a.im); }
+EB_HD double cabs(Cx a) { return hypot(a.re, a.im); }
+EB_HD double cabs2(Cx a) { return a.re * a.re + a.im * a.im; }
+EB_HD Cx operator/(Cx a, Cx b) {  // Smith's algorithm: no overflow in |b|^2
+    if (fabs(b.re) >= fabs(b.im)) {
+        const double r = b.im / b.re, d = b.re + b.im * r;
+        return cx((a.re + a.im * r) / d, (a.im - a.re * r) / d);
+    }
+    const double r = b.re / b.im, d = b.re * r + b.im;
+    return cx((a.re * r + a.im) / d, (a.im * r - a.re) / d);
+}
+EB_HD Cx csqrt_(Cx a) {  // principal square root
+    const double m = cabs(a);
+    if (m == 0.0) return cx(0.0, 0.0);
+    const double s = sqrt(0.5 * (m + fabs(a.re)));
+    const double t = 0.5 * a.im / s;
+    if (a.re >= 0.0) return cx(s, t);
+    return cx(fabs(t), a.im >= 0.0 ? s : -s);
+}
+
+// ---- Cholesky QR ------------------------------------------------------------------------------------
+// W (k x k Hermitian, only the upper triangle is read) = R^H R with R upper triangular, real positive
+// diagonal.  Returns false when a pivot falls below 1e-13 of its diagonal entry: the block has (numerically)
+// lost rank and R^{-1} would not orthonormalise it.
+EB_HDN bool chol_upper(const Cx* W, int k, Cx* R) {
+    for (int j = 0; j < k; ++j) {
+        double d = W[j * kBlockLd + j].re;
+        for (int p = 0; p < j; ++p) d -= cabs2(R[p * kBlockLd + j]);
+        const double wjj = W[j * kBlockLd + j].re;
+        if (!(d > 1e-13 * wjj) || !(wjj > 0.0) || !(wjj < HUGE_VAL)) return false;  // also NaN / inf / zero block
+        const double r = sqrt(d);
+        for (int c = 0; c < j; ++c) R[j * kBlockLd + c] = cx(0.0);
+        R[j * kBlockLd + j] = cx(r);
+        for (int c = j + 1; c < k; ++c) {
+            Cx s = W[j * kBlockLd + c];
+            for (int p = 0; p < j; ++p) s = s - conj(R[p * kBlockLd + j]) * R[p * kBlockLd + c];
+            R[j * kBlockLd + c] = cx(s.re / r, s.im / r);
+        }
+    }
+    return true;
+}
+
+// T = R^{-1}, R upper triangular with non-zero diagonal.
+EB_HDN void tri_inverse_upper(const Cx* R, int k, Cx* T) {
+    for (int c = 0; c < k; ++c) {
+        for (int r = c + 1; r < k; ++r) T[r * kBlockLd + c] = cx(0.0);
+        T[c * kBlockLd + c] = cx(1.0) / R[c * kBlockLd + c];
+        for (int r = c - 1; r >= 0; --r) {
+            Cx s = cx(0.0);
+            for (int p = r + 1; p <= c; ++p) s = s + R[r * kBlockLd + p] * T[p * kBlockLd + c];
+            T[r * kBlockLd + c] = -(s / R[r * kBlockLd + r]);
+        }
+    }
+}
+
+// ---- complex Schur decomposition of a small general matrix -------------------------------------------
+// Rotation G = [c s; -conj(s) c] (c real) with G [a; b] = [r; 0].
+EB_HD void givens(Cx a, Cx b, double& c, Cx& s) {
+    const double nb = cabs(b);
+    if (nb == 0.0) {
+        c = 1.0;
+        s = cx(0.0);
+        return;
+    }
+    const double na = cabs(a);
+    if (na == 0.0) {
+        c = 0.0;
+        s = cx(b.re / nb, -b.im / nb);
+        return;
+    }
+    const double nrm = hypot(na, nb);
+    c = na / nrm;
+    const Cx ph = cx(a.re / na, a.im / na);
+    s = ph * conj(b);
+    s = cx(s.re / nrm, s.im / nrm);
+}
+// rows (i, j) of M <- G * rows, columns q0..k-1
+EB_HD void rot_rows(Cx* M, int k, int i, int j, double c, Cx s, int q0) {
+    for (int q = q0; q < k; ++q) {
+        const Cx x = M[i * kBlockLd + q], y = M[j * kBlockLd + q];
+        M[i * kBlockLd + q] = c * x + s * y;
+        M[j * kBlockLd + q] = c * y - conj(s) * x;
+    }
+}
+// columns (i, j) of M <- columns * G^H, rows 0..p1-1
+EB_HD void rot_cols(Cx* M, int i, int j, double c, Cx s, int p1) {
+    for (int p = 0; p < p1; ++p) {
+        const Cx x = M[p * kBlockLd + i], y = M[p * kBlockLd + j];
+        M[p * kBlockLd + i] = c * x + conj(s) * y;
+        M[p * kBlockLd + j] = c * y - s * x;
+    }
+}
+
+// In place: M (general k x k) -> upper triangular Tm, Z unitary with M_in = Z Tm Z^H.  Returns false if
+// the QR iteration did not converge (60 sweeps on one eigenvalue).
+EB_HDN bool schur_complex(Cx* M, int k, Cx* Z) {
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) Z[i * kBlockLd + j] = cx(i == j ? 1.0 : 0.0);
+    // Hessenberg form by Givens similarity transforms
+    for (int j = 0; j + 2 < k; ++j)
+        for (int i = k - 1; i >= j + 2; --i) {
+            if (cabs(M[i * kBlockLd + j]) == 0.0) continue;
+            double c;
+            Cx s;
+            givens(M[(i - 1) * kBlockLd + j], M[i * kBlockLd + j], c, s);
+            rot_rows(M, k, i - 1, i, c, s, j);
+            M[i * kBlockLd + j] = cx(0.0);
+            rot_cols(M, i - 1, i, c, s, k);
+            rot_cols(Z, i - 1, i, c, s, k);
+        }
+    const double eps = 2.220446049250313e-16;
+    double norm = 0.0;
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) norm = fmax(norm, cabs(M[i * kBlockLd + j]));
+    int hi = k - 1, sweeps = 0;
+    double cs[kBlockMax];
+    Cx sn[kBlockMax];
+    while (hi > 0) {
+        int l = hi;
+        for (; l > 0; --l) {
+            const double sub = cabs(M[l * kBlockLd + l - 1]);
+            double diag = cabs(M[(l - 1) * kBlockLd + l - 1]) + cabs(M[l * kBlockLd + l]);
+            if (diag == 0.0) diag = norm;
+            if (sub <= eps * diag) {
+                M[l * kBlockLd + l - 1] = cx(0.0);
+                break;
+            }
+        }
+        if (l == hi) {  // M[hi][hi] is an eigenvalue
+            --hi;
+            sweeps = 0;
+            continue;
+        }
+        if (++sweeps > 60) return false;
+        // Wilkinson shift: the eigenvalue of the trailing 2 x 2 nearer to its last diagonal entry
+        const Cx a = M[(hi - 1) * kBlockLd + hi - 1], b = M[(hi - 1) * kBlockLd + hi];
+        const Cx c2 = M[hi * kBlockLd + hi - 1], d = M[hi * kBlockLd + hi];
+        Cx mu;
+        if (sweeps == 10 || sweeps == 20 || sweeps == 30) {
+            mu = cx(cabs(c2) + (hi >= 2 ? cabs(M[(hi - 1) * kBlockLd + hi - 2]) : 0.0)) + d;  // exceptional shift
+        } else {
+            const Cx half = 0.5 * (a - d);
+            const Cx disc = csqrt_(half * half + b * c2);
+            const Cx m1 = 0.5 * (a + d) + disc, m2 = 0.5 * (a + d) - disc;
+            mu = cabs(m1 - d) <= cabs(m2 - d) ? m1 : m2;
+        }
+        for (int i = l; i <= hi; ++i) M[i * kBlockLd + i] = M[i * kBlockLd + i] - mu;
+        for (int i = l; i < hi; ++i) {  // M - mu = Q R
+            givens(M[i * kBlockLd + i], M[(i + 1) * kBlockLd + i], cs[i], sn[i]);
+            rot_rows(M, k, i, i + 1, cs[i], sn[i], i);
+            M[(i + 1) * kBlockLd + i] = cx(0.0);
+        }
+        for (int i = l; i < hi; ++i) {  // R Q, and the rows above the window so the full Schur form is kept
+            rot_cols(M, i, i + 1, cs[i], sn[i], i + 2);
+            rot_cols(Z, i, i + 1, cs[i], sn[i], k);
+        }
+        for (int i = l; i <= hi; ++i) M[i * kBlockLd + i] = M[i * kBlockLd + i] + mu;
+    }
+    for (int i = 1; i < k; ++i)
+        for (int j = 0; j < i; ++j) M[i * kBlockLd + j] = cx(0.0);
+    return true;
+}
+
+// Order of the Ritz values: larger modulus first; moduli equal to 1e-9 relative (conjugate pairs, multiple
+// eigenvalues) are ordered by imaginary part, then real part, so the order is stable from trip to trip.
+EB_HD bool ritz_before(Cx a, Cx b) {
+    const double ma = cabs(a), mb = cabs(b), sc = fmax(ma, mb);
+    const double tie = 1e-9 * sc;
+    if (fabs(ma - mb) > tie) return ma > mb;
+    if (fabs(a.im - b.im) > tie) return a.im > b.im;
+    if (fabs(a.re - b.re) > tie) return a.re > b.re;
+    return false;
+}
+
+// Eigenvalues theta[0..k) (ordered by ritz_before) and unit-norm eigenvectors (columns of S, largest component
+// real and positive) of the general matrix H.  H is not modified.  false: the QR iteration failed.
+EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
+    Cx M[kBlockElems], Z[kBlockElems], V[kBlockElems];
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) M[i * kBlockLd + j] = H[i * kBlockLd + j];
+    if (!schur_complex(M, k, Z)) return false;
+    double norm = 0.0;
+    for (int i = 0; i < k; ++i)
+        for (int j = i; j < k; ++j) norm = fmax(norm, cabs(M[i * kBlockLd + j]));
+    const double small = fmax(norm * 2.220446049250313e-16, 1e-300);
+    // eigenvectors of the triangular factor: column i of V
+    for (int i = 0; i < k; ++i) {
+        const Cx lam = M[i * kBlockLd + i];
+        for (int r = i + 1; r < k; ++r) V[r * kBlockLd + i] = cx(0.0);
+        V[i * kBlockLd + i] = cx(1.0);
+        for (int r = i - 1; r >= 0; --r) {
+            Cx s = cx(0.0);
+            for (int p = r + 1; p <= i; ++p) s = s + M[r * kBlockLd + p] * V[p * kBlockLd + i];
+            Cx den = M[r * kBlockLd + r] - lam;
+            if (cabs(den) < small) den = cx(small);
+            V[r * kBlockLd + i] = -(s / den);
+        }
+    }
+    // order
+    int ord[kBlockMax];
+    for (int i = 0; i < k; ++i) ord[i] = i;
+    for (int i = 1; i < k; ++i) {  // insertion sort, stable
+        const int o = ord[i];
+        int j = i - 1;
+        while (j >= 0 && ritz_before(M[o * kBlockLd + o], M[ord[j] * kBlockLd + ord[j]])) {
+            ord[j + 1] = ord[j];
+            --j;
+        }
+        ord[j + 1] = o;
+    }
+    for (int c = 0; c < k; ++c) {
+        const int i = ord[c];
+        theta[c] = M[i * kBlockLd + i];
+        double n2 = 0.0, best = -1.0;
+        Cx big = cx(1.0);
+        for (int r = 0; r < k; ++r) {
+            Cx s = cx(0.0);
+            for (int p = 0; p <= i; ++p) s = s + Z[r * kBlockLd + p] * V[p * kBlockLd + i];
+            S[r * kBlockLd + c] = s;
+            const double a2 = cabs2(s);
+            n2 += a2;
+            if (a2 > best * (1.0 + 1e-12)) {  // first of (nearly) equal maxima: a stable choice
+                best = a2;
+                big = s;
+            }
+        }
+        const double nb = cabs(big);
+        const Cx ph = nb > 0.0 ? cx(big.re / nb, -big.im / nb) : cx(1.0);  // conj(big)/|big|
+        const double inv = n2 > 0.0 ? 1.0 / sqrt(n2) : 1.0;
+        for (int r = 0; r < k; ++r) S[r * kBlockLd + c] = inv * (ph * S[r * kBlockLd + c]);
+    }
+    return true;
+}
+
+// ---- the iteration state and its control step ---------------------------------------------------------
+enum { BSTOP_NONE = 0, BSTOP_CONVERGED = 1, BSTOP_BREAKDOWN = 2, BSTOP_MAX_TRIPS = 3 };
+
+struct BlockState {
+    int k;            // block width
+    int nev;          // Ritz values that must pass the convergence test (1 <= nev <= k)
+    int max_trips;    // opts.maxIterations
+    int launch_no;    // SpMM launches folded so far = number of the next launch; launch L reads U buffer L & 1
+    int iterations;   // usedIters (power_method.hpp:63)
+    int initialized;  // power_method.hpp:66
+    int converged;
+    int stop;         // BSTOP_*
+    int final_launch; // launch whose input block, T and S give the returned Ritz vectors: X = U T S
+    int reserved;
+    double tol;       // opts.tolerance
+    double sigma;     // power-of-two prescale of A (U_{m+1} = sigma A Q_m), H = C / sigma
+    Cx theta[kBlockMax];        // current Ritz values, ordered
+    Cx T[2][kBlockElems];       // T[L & 1] = R^{-1} used by launch L
+    Cx S[kBlockElems];          // Ritz vectors of H_{final_launch} in the Q basis
+    Cx H[kBlockElems];          // H of the last folded launch (diagnostics / tests)
+};
+
+EB_HD bool block_close_relative(Cx a, Cx b, double tol) {  // tolerance.hpp:28-33, a = new value
+    return cabs(a - b) <= tol * (1.0 + cabs(a));
+}
+
+// After the Gram pass over the start block: W = U_0^H U_0.
+EB_HDN void block_control_begin(BlockState* st, const Cx* W) {
+    Cx R[kBlockElems];
+    st->launch_no = 0;
+    st->iterations = 0;
+    st->initialized = 0;
+    st->converged = 0;
+    st->stop = BSTOP_NONE;
+    st->final_launch = -1;
+    for (int i = 0; i < st->k; ++i) st->theta[i] = cx(0.0);  // Scalar lambda = Scalar(0), power_method.hpp:61
+    for (int i = 0; i < kBlockElems; ++i) st->S[i] = cx((i / kBlockLd) == (i % kBlockLd) ? 1.0 : 0.0);
+    if (!chol_upper(W, st->k, R)) {
+        st->stop = BSTOP_BREAKDOWN;
+        return;
+    }
+    tri_inverse_upper(R, st->k, st->T[0]);
+    if (st->max_trips <= 0) st->stop = BSTOP_MAX_TRIPS;
+}
+
+// After SpMM launch L = st->launch_no:  C = Q_L^H (sigma A Q_L),  W = U_{L+1}^H U_{L+1}.
+// Launch 0 is the set-up product A Q_0 (the reference never forms x0^H A x0); launch L >= 1 closes trip
+// L - 1 of power_method.hpp:68-96 for every wanted Ritz value.
+EB_HDN void block_control_step(BlockState* st, const Cx* C, const Cx* W) {
+    const int k = st->k, L = st->launch_no;
+    const double inv_sigma = 1.0 / st->sigma;
+    Cx theta[kBlockMax];
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) st->H[i * kBlockLd + j] = inv_sigma * C[i * kBlockLd + j];
+    st->launch_no = L + 1;
+    if (!eig_general(st->H, k, theta, st->S)) {
+        st->stop = BSTOP_BREAKDOWN;
+        return;
+    }
+    st->final_launch = L;
+    if (L >= 1) {
+        bool all_close = st->initialized != 0;
+        for (int i = 0; i < st->nev && all_close; ++i) all_close = block_close_relative(theta[i], st->theta[i], st->tol);
+        for (int i = 0; i < k; ++i) st->theta[i] = theta[i];
+        st->iterations = L;  // usedIters = k + 1 with trip k = L - 1
+        if (all_close) {
+            st->converged = 1;
+            st->stop = BSTOP_CONVERGED;
+            return;
+        }
+        st->initialized = 1;
+        if (st->iterations >= st->max_trips) {
+            st->stop = BSTOP_MAX_TRIPS;
+            return;
+        }
+    }
+    Cx R[kBlockElems];
+    if (!chol_upper(W, k, R)) {  // A Q lost rank: the block counterpart of normY == 0 (power_method.hpp:73-76)
+        st->stop = BSTOP_BREAKDOWN;
+        return;
+    }
+    tri_inverse_upper(R, k, st->T[(L + 1) & 1]);
+}
+
+// M = T S (k x k): the returned Ritz vectors are X = U M.
+EB_HD void block_result_transform(const BlockState* st, Cx* M) {
+    const int k = st->k;
+    const Cx* T = st->T[(st->final_launch < 0 ? 0 : st->final_launch) & 1];
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) {
+            Cx s = cx(0.0);
+            for (int p = i; p < k; ++p) s = s + T[i * kBlockLd + p] * st->S[p * kBlockLd + j];
+            M[i * kBlockLd + j] = s;
+        }
+}
+
+}  // namespace eigsol_b200
