@@ -193,6 +193,26 @@ EIGSOL_B200_API int eigsol_b200_matvec(eigsol_b200_matrix* m, const void* x, voi
 EIGSOL_B200_API int eigsol_b200_rayleigh(eigsol_b200_matrix* m, const void* x, double dot_out[2],
                                          double* norm2_out);
 
+/* Block (simultaneous) power iteration: `block` vectors advance per pass over A (no
+ * counterpart in the reference, whose powerMethod keeps one vector, src/power_method/power_method.hpp:68-96).
+ *     Q = orth(U),  U <- A Q,  H = Q^H A Q (block x block),  Ritz values = eig(H), ordered by modulus
+ * With block = 1 this is the reference's loop trip for trip (same usedIters, flag, eigenvalue, vector).  A trip
+ * is one SpMM launch + one single-CTA control launch; convergence = the first `nev` Ritz values each pass
+ * is_close_relative (src/core/tolerance.hpp:28-33) against the previous trip.
+ *   block        1, 2, 4 or 8;  1 <= nev <= block
+ *   x0           n x block start block, column-major (Eigen's default), full column rank
+ *   x_out        n x block unit-norm Ritz vectors, column-major, or NULL.  dtype F64 with a complex-conjugate
+ *                pair of Ritz values in columns j, j+1 returns Re and Im of the pair's vector there (dgeev style)
+ *   lambda_out   2 * block doubles: (re, im) of each Ritz value
+ *   breakdown_out  1 if the block lost rank (A Q or x0 rank deficient -- the block counterpart of ||y|| == 0,
+ *                power_method.hpp:73-76); results are those of the last good trip
+ *   ms_out       device time of the iteration loop
+ * One GPU (comm == NULL matrices); any of the out pointers except lambda_out may be NULL. */
+EIGSOL_B200_API int eigsol_b200_block_power_run(eigsol_b200_matrix* m, int block, int nev, const void* x0,
+                                                int max_iterations, double tolerance, void* x_out,
+                                                double* lambda_out, int* iterations_out, int* converged_out,
+                                                int* breakdown_out, float* ms_out);
+
 /* Total kernel launches this handle has issued (bench.py's gpu_launches claim). */
 EIGSOL_B200_API int64_t eigsol_b200_matrix_launch_count(const eigsol_b200_matrix* m);
 

@@ -27,6 +27,7 @@ from ._capi import (C128, F64, KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_STREAM
                     KERNEL_NAMES, KERNEL_SELL, EigsolB200Error)
 
 __all__ = ["Matrix", "SolverOptions", "EigenResult", "powerMethod", "power_method", "DeviceMatrix", "Comm",
+           "BlockEigenResult", "blockPowerMethod", "random_block",
            "random_unit", "srand", "device_count", "EigsolB200Error", "readMatrixFromFile",
            "writeMatrixBinary", "readMatrixBinary"]
 
@@ -46,6 +47,18 @@ class EigenResult:
     eigenvector: np.ndarray = field(default_factory=lambda: np.zeros(0))
     iterations: int = 0
     converged: bool = False
+
+
+@dataclass
+class BlockEigenResult:
+    """Result of the block power iteration: the block's Ritz values ordered by modulus (the first ``nev`` passed
+    the convergence test), unit-norm Ritz vectors as columns, trips, flags."""
+    eigenvalues: np.ndarray = field(default_factory=lambda: np.zeros(0, dtype=np.complex128))
+    eigenvectors: np.ndarray = field(default_factory=lambda: np.zeros((0, 0)))
+    iterations: int = 0
+    converged: bool = False
+    breakdown: bool = False
+    device_ms: float = 0.0
 
 
 def device_count() -> int:
@@ -189,6 +202,30 @@ def powerMethod(M: Matrix, opts: SolverOptions | None = None, scalar=None, x0: n
 
 
 power_method = powerMethod
+
+
+def random_block(n: int, k: int, dtype=np.float64, seed: int = 1) -> np.ndarray:
+    """n x k start block: column j is the reference's start vector (power_method.hpp:62) drawn after srand(seed + j)."""
+    return np.asfortranarray(np.stack([random_unit(n, dtype, seed + j) for j in range(k)], axis=1))
+
+
+def blockPowerMethod(M: Matrix, block: int = 4, nev: int | None = None, opts: SolverOptions | None = None,
+                     x0: np.ndarray | None = None) -> BlockEigenResult:
+    """Block (simultaneous) power iteration on the B200: ``block`` vectors per pass over the matrix, Rayleigh-Ritz
+    on the block (not in the reference API).  Same checks and messages as powerMethod
+    (power_method.hpp:52-58); with ``block = 1`` it returns what powerMethod returns."""
+    n, ncols = M.rows(), M.cols()
+    if n != ncols:
+        raise RuntimeError("powerMethod: matrix must be square")
+    if n == 0:
+        raise RuntimeError("powerMethod: matrix has zero size")
+    if x0 is None:
+        x0 = random_block(n, block, M.scalar_type())
+    dm = DeviceMatrix.from_matrix(M)
+    try:
+        return dm.block_power(x0, nev, opts)
+    finally:
+        dm.close()
 
 
 # --------------------------------------------------------------------------------------------------
@@ -381,6 +418,21 @@ class DeviceMatrix:
         _capi.check(_capi.lib().eigsol_b200_rayleigh(self._h, _capi.ptr(self._vec(x)), dot, C.byref(nrm)))
         d = complex(dot[0], dot[1])
         return (d if np.issubdtype(self.dtype, np.complexfloating) else d.real), float(nrm.value)
+
+    def block_power(self, x0, nev: int | None = None, opts: SolverOptions | None = None, want_vectors: bool = True) -> BlockEigenResult:
+        """Block power iteration (eigsol_b200_block_power_run): ``x0`` is the n x k start block, k in {1, 2, 4, 8}."""
+        opts = opts or SolverOptions()
+        x0 = np.asfortranarray(np.asarray(x0, dtype=self.dtype).reshape(self.n, -1))
+        k = x0.shape[1]
+        nev = k if nev is None else int(nev)
+        x = np.empty((self.n, k), dtype=self.dtype, order="F") if want_vectors else None
+        lam = np.zeros(2 * k)
+        iters, conv, brk, ms = C.c_int(0), C.c_int(0), C.c_int(0), C.c_float(0)
+        _capi.check(_capi.lib().eigsol_b200_block_power_run(
+            self._h, k, nev, _capi.ptr(x0), int(opts.maxIterations), float(opts.tolerance),
+            _capi.ptr(x) if want_vectors else None, _capi.ptr(lam), C.byref(iters), C.byref(conv), C.byref(brk), C.byref(ms)))
+        return BlockEigenResult(lam.view(np.complex128).copy(), x if want_vectors else np.zeros((0, 0)), int(iters.value),
+                                bool(conv.value), bool(brk.value), float(ms.value))
 
     def close(self):
         if self._h:

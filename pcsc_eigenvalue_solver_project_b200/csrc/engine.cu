@@ -1379,6 +1379,8 @@ void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
 
 }  // namespace eigsol_b200
 
+#include "block_host.cuh"
+
 // =================================================================================================
 // C ABI
 // =================================================================================================
@@ -1644,6 +1646,22 @@ int eigsol_b200_rayleigh(eigsol_b200_matrix* m, const void* x, double dot_out[2]
             dot_out[1] = o[1];
         }
         if (norm2_out) *norm2_out = o[2];
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_block_power_run(eigsol_b200_matrix* m, int block, int nev, const void* x0, int max_iterations,
+                                double tolerance, void* x_out, double* lambda_out, int* iterations_out,
+                                int* converged_out, int* breakdown_out, float* ms_out) {
+    if (!m || !x0 || !lambda_out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    std::lock_guard<std::mutex> lock(g_api_mutex);
+    return guarded([&] {
+        BlockResult r;
+        block_power_run(m->impl, block, nev, x0, max_iterations, tolerance, x_out, lambda_out, r);
+        if (iterations_out) *iterations_out = r.iterations;
+        if (converged_out) *converged_out = r.converged;
+        if (breakdown_out) *breakdown_out = r.breakdown;
+        if (ms_out) *ms_out = r.ms;
         return int(EIGSOL_B200_OK);
     });
 }
