@@ -191,6 +191,301 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_block_kernel(CsrView<S> A, Blo
     block_cta_reduce<S, K, BLOCK>(acc, ba.partials, ba.nslots, blockIdx.x);
 }
 
+// =================================================================================================
+// SpMM, CSR, K lanes per row: lane b of a row's lane group owns column b of the block.  A matrix entry is
+// loaded once per group (same address in K lanes = one transaction) and its K operands U[col, 0..K) are one
+// coalesced 8K-byte piece across the group.  A lane keeps ONE running product and 2K Gram sums, so the
+// register count stays near 64 for every K (the thread-per-row kernel above needs 100 registers at K = 4 and
+// spills at K = 8: too few warps in flight to cover the col -> U[col] load chain), and the entry loop is
+// unrolled UNROLL-wide with all gathers of a chunk issued before the first use.
+// Work unit = BLOCK / K consecutive rows.  The epilogue moves y and own across the group with shuffles.
+// =================================================================================================
+template <class S> __device__ __forceinline__ S shfl_grp(S v, int src, int width);
+template <> __device__ __forceinline__ double shfl_grp<double>(double v, int src, int width) {
+    return __shfl_sync(0xffffffffu, v, src, width);
+}
+template <> __device__ __forceinline__ double2 shfl_grp<double2>(double2 v, int src, int width) {
+    return make_double2(__shfl_sync(0xffffffffu, v.x, src, width), __shfl_sync(0xffffffffu, v.y, src, width));
+}
+__device__ __forceinline__ double shfl_xor_d(double v, int d) { return __shfl_xor_sync(0xffffffffu, v, d); }
+
+// Sums held as: lane (g, b) has c[a] = sum over its rows of conj(q_a) v_b and w[a] = sum of conj(v_a) v_b.
+template <class S, int K, int BLOCK>
+__device__ __forceinline__ void block_cta_reduce_lanes(const S (&c)[K], const S (&w)[K], double* __restrict__ partials,
+                                                       int nslots, int slot) {
+    constexpr int NE = BlockSums<K>::NE, NC = BlockSums<K>::NC, STRIDE = BlockStride<S, K>::value;
+    __shared__ double sred[BLOCK / 32][STRIDE];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, b = lane % K;
+#pragma unroll
+    for (int comp = 0; comp < STRIDE / NE; ++comp) {
+#pragma unroll
+        for (int a = 0; a < K; ++a) {
+            double vc = comp_of(c[a], comp), vw = comp_of(w[a], comp);
+#pragma unroll
+            for (int d = 16; d >= K; d >>= 1) {  // lanes with the same b: b, b + K, b + 2K, ...
+                vc += shfl_xor_d(vc, d);
+                vw += shfl_xor_d(vw, d);
+            }
+            if (lane < K) {
+                sred[warp][comp * NE + a * K + b] = vc;
+                if (a <= b) sred[warp][comp * NE + NC + a * K - a * (a - 1) / 2 + (b - a)] = vw;
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < STRIDE; i += BLOCK) {
+        double s = 0.0;
+#pragma unroll
+        for (int wp = 0; wp < BLOCK / 32; ++wp) s += sred[wp][i];
+        partials[int64_t(i) * nslots + slot] = s;
+    }
+}
+
+template <class S, int K, int BLOCK, int UNROLL>
+__global__ void __launch_bounds__(BLOCK) spmm_csr_lanes_kernel(CsrView<S> A, BlockArgs<S> ba) {
+    constexpr int RPU = BLOCK / K;  // rows per unit
+    __shared__ S sT[K * K];
+    const BlockState* st = ba.st;
+    if (st->stop != BSTOP_NONE) return;
+    const int L = st->launch_no;
+    const double sigma = st->sigma;
+    const S* __restrict__ U = ba.u[L & 1];
+    S* __restrict__ out = ba.u[(L + 1) & 1];
+    load_T<S, K>(st, L, sT);
+    __syncthreads();
+    const int grp = threadIdx.x / K, b = threadIdx.x % K;
+    S tcol[K];  // column b of T (zero below the diagonal)
+#pragma unroll
+    for (int a = 0; a < K; ++a) tcol[a] = sT[a * K + b];
+    S cacc[K], wacc[K];
+#pragma unroll
+    for (int a = 0; a < K; ++a) cacc[a] = wacc[a] = Sc<S>::zero();
+    const int nunits = (A.rows + RPU - 1) / RPU;
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+        const int row = unit * RPU + grp;
+        const bool valid = row < A.rows;
+        const int safe = valid ? row : 0;
+        const int p0 = valid ? __ldg(A.rowptr + row) : 0, p1 = valid ? __ldg(A.rowptr + row + 1) : 0;
+        S y = Sc<S>::zero();
+        for (int p = p0; p < p1; p += UNROLL) {
+            int col[UNROLL];
+            S a[UNROLL], u[UNROLL];
+#pragma unroll
+            for (int i = 0; i < UNROLL; ++i) {
+                const bool ok = p + i < p1;
+                col[i] = ok ? __ldg(A.colidx + p + i) : safe;
+                a[i] = ok ? __ldg(A.vals + p + i) : Sc<S>::zero();
+            }
+#pragma unroll
+            for (int i = 0; i < UNROLL; ++i) u[i] = __ldg(U + int64_t(col[i]) * K + b);
+#pragma unroll
+            for (int i = 0; i < UNROLL; ++i) Sc<S>::mac(y, a[i], u[i]);
+        }
+        const S own = valid ? __ldg(U + int64_t(row) * K + b) : Sc<S>::zero();
+        S q = Sc<S>::zero(), v = Sc<S>::zero();
+#pragma unroll
+        for (int a = 0; a < K; ++a) {
+            Sc<S>::mac(v, shfl_grp<S>(y, a, K), tcol[a]);
+            Sc<S>::mac(q, shfl_grp<S>(own, a, K), tcol[a]);
+        }
+        v = Sc<S>::scale(v, sigma);
+        if (valid) out[int64_t(row) * K + b] = v;
+#pragma unroll
+        for (int a = 0; a < K; ++a) {
+            cmac(cacc[a], shfl_grp<S>(q, a, K), v);
+            cmac(wacc[a], shfl_grp<S>(v, a, K), v);
+        }
+    }
+    block_cta_reduce_lanes<S, K, BLOCK>(cacc, wacc, ba.partials, ba.nslots, blockIdx.x);
+}
+
+// =================================================================================================
+// SpMM, CSR, real K = 4 / 8: the kernel the dispatcher uses for wide real blocks.
+// What limits the two kernels above at K >= 4 is not HBM but the L1 data stage (distinct 128-byte lines per
+// warp instruction) and, for the lane kernel, the 4K shuffles per row.  Here
+//   * the unit's matrix entries (256 rows) are staged in shared memory by fully coalesced loads -- the
+//     thread-per-row walk of vals / colidx costs ~4.6 line accesses per row, the staged copy 0.7;
+//   * a lane owns FOUR columns of a row (K / 4 lanes per row) and fetches them with one 256-bit load, so a
+//     warp's gather of a stencil neighbour touches each line once;
+//   * the Gram sums C = Q^H V and W = V^H V run on the fp64 tensor cores: q and v go through a per-warp
+//     shared tile and every 4 rows are one (K = 4: C and W stacked in one 8 x 8 tile) or two (K = 8)
+//     mma.m8n8k4.f64 -- no shuffles, and ~60 accumulator registers fewer than the thread-per-row kernel.
+// =================================================================================================
+__device__ __forceinline__ void ld_nc_f64x4(const double* p, double (&o)[4]) {
+    asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p));
+}
+__device__ __forceinline__ void st_f64x4(double* p, const double (&v)[4]) {
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
+}
+// D (8 x 8) += A (8 x 4, row) * B (4 x 8, col); lane l holds A[l/4][l%4], B[l%4][l/4], D[l/4][2(l%4) + {0,1}]
+__device__ __forceinline__ void dmma_8x8x4(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(d0), "+d"(d1)
+                 : "d"(a), "d"(b));
+}
+
+template <int K, int BLOCK>
+__global__ void __launch_bounds__(BLOCK) spmm_csr_tile_kernel(CsrView<double> A, BlockArgs<double> ba) {
+    static_assert(K == 4 || K == 8, "tile kernel: K = 4 or 8");
+    constexpr int LPR = K / 4;          // lanes per row
+    constexpr int RPP = BLOCK / LPR;    // rows per CTA pass
+    constexpr int UR = 256;             // rows per unit (staged together)
+    constexpr int PASSES = UR / RPP;
+    constexpr int CAP = 2048;           // staged entries per unit; a unit with more reads the matrix from global
+    constexpr int RW = 32 / LPR;        // rows per warp pass
+    constexpr int TW = 2 * K;           // tile row: q[0..K) then v[0..K)
+    constexpr int NE = BlockSums<K>::NE, NC = BlockSums<K>::NC;
+    __shared__ double sT[K * K];
+    __shared__ double sval[CAP];
+    __shared__ int scol[CAP];
+    __shared__ int srp[UR + 1];
+    __shared__ __align__(16) double tile[BLOCK / 32][RW * TW];
+    __shared__ double sred[BLOCK / 32][NE];
+    const BlockState* st = ba.st;
+    if (st->stop != BSTOP_NONE) return;
+    const int L = st->launch_no;
+    const double sigma = st->sigma;
+    const double* __restrict__ U = ba.u[L & 1];
+    double* __restrict__ out = ba.u[(L + 1) & 1];
+    load_T<double, K>(st, L, sT);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = threadIdx.x % LPR;        // which 4 columns of the row this lane owns
+    const int fr = lane & 3, fc = lane >> 2;  // mma fragment coordinates
+    double* wt = tile[warp];
+    // accumulators: K = 8: (c0, c1) = C fragment, (w0, w1) = W fragment; K = 4: (c0, c1) = the stacked 8 x 8 tile
+    double c0 = 0.0, c1 = 0.0, w0 = 0.0, w1 = 0.0;
+    const int nunits = (A.rows + UR - 1) / UR;
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+        const int r0 = unit * UR, nr = min(UR, A.rows - r0);
+        __syncthreads();  // the previous unit's readers are done with the staged arrays
+        for (int i = threadIdx.x; i <= nr; i += BLOCK) srp[i] = __ldg(A.rowptr + r0 + i);
+        __syncthreads();
+        const int e0 = srp[0], ne = srp[nr] - e0;
+        const bool staged = ne <= CAP;
+        if (staged)
+            for (int i = threadIdx.x; i < ne; i += BLOCK) {
+                sval[i] = ld_stream_f64(A.vals + e0 + i);
+                scol[i] = ld_stream_s32(A.colidx + e0 + i);
+            }
+        __syncthreads();
+#pragma unroll 1
+        for (int pass = 0; pass < PASSES; ++pass) {
+            const int lr = pass * RPP + threadIdx.x / LPR, row = r0 + lr;
+            const bool valid = lr < nr;
+            double y[4] = {0.0, 0.0, 0.0, 0.0}, own[4] = {0.0, 0.0, 0.0, 0.0};
+            if (valid) {
+                const int p0 = srp[lr] - e0, p1 = srp[lr + 1] - e0;
+                int p = p0;
+                for (; p + 1 < p1; p += 2) {  // two gathers in flight
+                    const int ca = staged ? scol[p] : __ldg(A.colidx + e0 + p);
+                    const int cb = staged ? scol[p + 1] : __ldg(A.colidx + e0 + p + 1);
+                    const double va = staged ? sval[p] : __ldg(A.vals + e0 + p);
+                    const double vb = staged ? sval[p + 1] : __ldg(A.vals + e0 + p + 1);
+                    double ua[4], ub[4];
+                    ld_nc_f64x4(U + int64_t(ca) * K + 4 * sub, ua);
+                    ld_nc_f64x4(U + int64_t(cb) * K + 4 * sub, ub);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) y[j] = fma(va, ua[j], y[j]);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) y[j] = fma(vb, ub[j], y[j]);
+                }
+                if (p < p1) {
+                    const int ca = staged ? scol[p] : __ldg(A.colidx + e0 + p);
+                    const double va = staged ? sval[p] : __ldg(A.vals + e0 + p);
+                    double ua[4];
+                    ld_nc_f64x4(U + int64_t(ca) * K + 4 * sub, ua);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) y[j] = fma(va, ua[j], y[j]);
+                }
+                ld_nc_f64x4(U + int64_t(row) * K + 4 * sub, own);
+            }
+            // the whole row of y and own in every lane of the row's lane group
+            double yf[K], of[K];
+            if constexpr (LPR == 1) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    yf[j] = y[j];
+                    of[j] = own[j];
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const double yo = __shfl_xor_sync(0xffffffffu, y[j], 1), oo = __shfl_xor_sync(0xffffffffu, own[j], 1);
+                    yf[j] = sub == 0 ? y[j] : yo;
+                    yf[4 + j] = sub == 0 ? yo : y[j];
+                    of[j] = sub == 0 ? own[j] : oo;
+                    of[4 + j] = sub == 0 ? oo : own[j];
+                }
+            }
+            double v[4], q[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                double vv = 0.0, qq = 0.0;
+#pragma unroll
+                for (int a = 0; a < K; ++a) {
+                    const double t = sT[a * K + 4 * sub + j];  // zero below the diagonal
+                    vv = fma(yf[a], t, vv);
+                    qq = fma(of[a], t, qq);
+                }
+                v[j] = vv * sigma;
+                q[j] = qq;
+            }
+            if (valid) st_f64x4(out + int64_t(row) * K + 4 * sub, v);
+            // q and v of the warp's RW rows into its tile (zeros for rows past the end), then the Gram updates
+            double* tr = wt + (lane / LPR) * TW;
+            *reinterpret_cast<double4*>(tr + 4 * sub) = make_double4(q[0], q[1], q[2], q[3]);
+            *reinterpret_cast<double4*>(tr + K + 4 * sub) = make_double4(v[0], v[1], v[2], v[3]);
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < RW / 4; ++j) {
+                const double* r4 = wt + (4 * j + fr) * TW;
+                if constexpr (K == 8) {
+                    const double qa = r4[fc], vb = r4[K + fc];
+                    dmma_8x8x4(c0, c1, qa, vb);  // C += Q^T V
+                    dmma_8x8x4(w0, w1, vb, vb);  // W += V^T V
+                } else {
+                    const double a8 = r4[fc];            // rows of A: q_0..q_3, v_0..v_3
+                    const double b8 = r4[(fc + 4) & 7];  // columns of B: v_0..v_3, q_0..q_3
+                    dmma_8x8x4(c0, c1, a8, b8);          // top-left 4 x 4 = Q^T V, bottom-left = V^T V
+                }
+            }
+            __syncwarp();
+        }
+    }
+    // fragments -> entries.  Lane holds D[fc][2 fr], D[fc][2 fr + 1].
+    for (int i = lane; i < NE; i += 32) sred[warp][i] = 0.0;
+    __syncwarp();
+    if constexpr (K == 8) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int a = fc, b = 2 * fr + h;
+            sred[warp][a * K + b] = h ? c1 : c0;
+            if (a <= b) sred[warp][NC + a * K - a * (a - 1) / 2 + (b - a)] = h ? w1 : w0;
+        }
+    } else {
+        if (fr < 2) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int b = 2 * fr + h;
+                const double d = h ? c1 : c0;
+                if (fc < 4) {
+                    sred[warp][fc * K + b] = d;
+                } else {
+                    const int a = fc - 4;
+                    if (a <= b) sred[warp][NC + a * K - a * (a - 1) / 2 + (b - a)] = d;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < NE; i += BLOCK) {
+        double s = 0.0;
+#pragma unroll
+        for (int wp = 0; wp < BLOCK / 32; ++wp) s += sred[wp][i];
+        ba.partials[int64_t(i) * ba.nslots + blockIdx.x] = s;
+    }
+}
+
 // W = U^H U of the start block (C is left zero): same reduction, no matrix.
 template <class S, int K, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) block_gram_kernel(const S* __restrict__ U, int64_t rows, double* partials, int nslots) {

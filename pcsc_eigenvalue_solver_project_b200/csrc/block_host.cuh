@@ -29,6 +29,7 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
 
     // launch geometry
     int grid, ntiles = 1, nseg = 1, grid_partial = 0;
+    void (*spmm)(CsrView<S>, BlockArgs<S>) = nullptr;
     if (m.dense) {
         grid = int(std::min<int64_t>((n + B - 1) / B, int64_t(m.sm_count) * occupancy(block_combine_kernel<S, K, B>, B)));
         const int rt = B * DenseRpt<S>::value;
@@ -38,8 +39,32 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
         grid_partial = ntiles * nseg;
         d_dpart.alloc(size_t(nseg) * size_t(n) * K * s);
     } else {
-        const int occ = occupancy(spmm_csr_block_kernel<S, K, B>, B);
-        grid = int(std::min<int64_t>((n + B - 1) / B, int64_t(m.sm_count) * occ));
+        // real K >= 4: staged tile kernel; complex K >= 4: K lanes per row; K <= 2: one thread per row (block.cuh).
+        // EIGSOL_B200_BLOCK_KERNEL=row|lanes|tile overrides.
+        enum { V_ROW, V_LANES, V_TILE };
+        constexpr bool can_tile = !Sc<S>::is_complex && K >= 4, can_row = K <= 4;
+        int variant = can_tile ? V_TILE : (K >= 4 ? V_LANES : V_ROW);
+        if (const char* kv = std::getenv("EIGSOL_B200_BLOCK_KERNEL")) {
+            if (!std::strcmp(kv, "row")) variant = V_ROW;
+            else if (!std::strcmp(kv, "lanes")) variant = V_LANES;
+            else if (!std::strcmp(kv, "tile")) variant = V_TILE;
+        }
+        if (variant == V_TILE && !can_tile) variant = K >= 4 ? V_LANES : V_ROW;
+        if (variant == V_ROW && !can_row) variant = V_LANES;
+        const int unroll = env_int("EIGSOL_B200_BLOCK_UNROLL", 4);
+        int rows_per_unit = B;
+        if (variant == V_TILE) {
+            if constexpr (can_tile) spmm = spmm_csr_tile_kernel<K, B>;
+            rows_per_unit = 256;
+        } else if (variant == V_LANES) {
+            spmm = unroll >= 8 ? spmm_csr_lanes_kernel<S, K, B, 8>
+                               : (unroll <= 2 ? spmm_csr_lanes_kernel<S, K, B, 2> : spmm_csr_lanes_kernel<S, K, B, 4>);
+            rows_per_unit = B / K;
+        } else {
+            if constexpr (can_row) spmm = spmm_csr_block_kernel<S, K, B>;
+        }
+        const int occ = occupancy(spmm, B);
+        grid = int(std::min<int64_t>((n + rows_per_unit - 1) / rows_per_unit, int64_t(m.sm_count) * occ));
     }
     grid = std::max(grid, 1);
     constexpr int stride = BlockStride<S, K>::value;
@@ -77,7 +102,7 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
             res.launches += 3;
         } else {
             CsrView<S> A{int32_t(n), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
-            spmm_csr_block_kernel<S, K, B><<<grid, B, 0, st>>>(A, ba);
+            spmm<<<grid, B, 0, st>>>(A, ba);
             res.launches += 2;
         }
         block_control_kernel<1024><<<1, 1024, 0, st>>>(ba.st, ba.partials, grid, K, Sc<S>::is_complex ? 1 : 0, 0);
@@ -151,7 +176,6 @@ static void block_run_k(MatrixImpl& m, int k, int nev, const void* x0, int max_i
 static void block_power_run(MatrixImpl& m, int k, int nev, const void* x0, int max_it, double tol, void* x_out,
                             double* lambda_out, BlockResult& res) {
     if (m.nranks != 1) throw PlanError("the block power iteration runs on one GPU in this version");
-    if (m.begun) throw StateError("eigsol_b200: a stepwise solve is in progress on this matrix");
     if (nev < 1 || nev > k) throw PlanError("nev must satisfy 1 <= nev <= block width");
     if (!x0 || !lambda_out) throw PlanError("null pointer");
     EIGSOL_CUDA(cudaSetDevice(m.device));

