@@ -23,7 +23,18 @@ template <class S> struct BlockArgs {
     BlockState* st;
     double* partials;   // [entry][slot]
     int nslots;
+    int chunk;          // SpMM kernels: units are dealt to the CTAs in runs of `chunk` consecutive units
 };
+
+// Block-cyclic unit order: CTA b works on units (g * grid + b) * chunk + j, j = 0..chunk-1, g = 0, 1, ...
+// Consecutive units of a run share their near-diagonal operand rows through L1 (a stencil's +-1 line
+// neighbours), while the CTAs running at the same time stay within grid * chunk units of each other, so the
+// far neighbours (+-1 plane) are still shared through L2.  -1 past the end.
+__device__ __forceinline__ int block_unit_at(int it, int chunk, int nunits) {
+    const int g = it / chunk, j = it - g * chunk;
+    const long long u = (long long)(g * int(gridDim.x) + int(blockIdx.x)) * chunk + j;
+    return u < nunits ? int(u) : -1;
+}
 
 // number of accumulated sums: C (K x K) and the upper triangle of W
 template <int K> struct BlockSums {
@@ -168,7 +179,7 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_block_kernel(CsrView<S> A, Blo
     BlockAcc<S, K> acc;
     acc.clear();
     const int nunits = (A.rows + BLOCK - 1) / BLOCK;
-    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+    for (int it = 0, unit; (unit = block_unit_at(it, ba.chunk, nunits)) >= 0; ++it) {
         const int row = unit * BLOCK + threadIdx.x;
         if (row < A.rows) {
             const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
@@ -261,7 +272,7 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_lanes_kernel(CsrView<S> A, Blo
 #pragma unroll
     for (int a = 0; a < K; ++a) cacc[a] = wacc[a] = Sc<S>::zero();
     const int nunits = (A.rows + RPU - 1) / RPU;
-    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+    for (int it = 0, unit; (unit = block_unit_at(it, ba.chunk, nunits)) >= 0; ++it) {
         const int row = unit * RPU + grp;
         const bool valid = row < A.rows;
         const int safe = valid ? row : 0;
@@ -307,9 +318,9 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_lanes_kernel(CsrView<S> A, Blo
 //     thread-per-row walk of vals / colidx costs ~4.6 line accesses per row, the staged copy 0.7;
 //   * a lane owns FOUR columns of a row (K / 4 lanes per row) and fetches them with one 256-bit load, so a
 //     warp's gather of a stencil neighbour touches each line once;
-//   * the Gram sums C = Q^H V and W = V^H V run on the fp64 tensor cores: q and v go through a per-warp
-//     shared tile and every 4 rows are one (K = 4: C and W stacked in one 8 x 8 tile) or two (K = 8)
-//     mma.m8n8k4.f64 -- no shuffles, and ~60 accumulator registers fewer than the thread-per-row kernel.
+//   * the Gram sums C = Q^H V and W = V^H V: K = 4 keeps the 26 sums of a thread's rows in registers;
+//     K = 8 (100 sums: too many registers) runs them on the fp64 tensor cores -- q and v go through a
+//     per-warp shared tile and every 4 rows are two mma.m8n8k4.f64, no shuffles.
 // =================================================================================================
 __device__ __forceinline__ void ld_nc_f64x4(const double* p, double (&o)[4]) {
     asm volatile("ld.global.nc.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p));
@@ -324,22 +335,63 @@ __device__ __forceinline__ void dmma_8x8x4(double& d0, double& d1, double a, dou
                  : "d"(a), "d"(b));
 }
 
-template <int K, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) spmm_csr_tile_kernel(CsrView<double> A, BlockArgs<double> ba) {
+__device__ __forceinline__ void mbar_expect(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_copy_1d(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_addr(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+
+// mbar_wait with a watchdog: a byte-count mismatch would otherwise spin forever; after ~2 s the kernel traps and
+// the host sees a launch failure instead of a hung GPU.
+__device__ __forceinline__ void mbar_wait_bounded(unsigned long long* bar, unsigned parity) {
+    const long long t0 = clock64();
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_addr(bar)), "r"(parity)
+            : "memory");
+        if (!done && clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+
+// Shared-memory stage of one unit: the unit's row pointers, values and column indices, copied by the TMA
+// engine (cp.async.bulk, 16-byte aligned source ranges, completion on an mbarrier) while the CTA computes the
+// previous unit.  Two stages.
+template <int UR> struct TileStage {
+    static constexpr int RP = UR + 4;  // row pointers (+ alignment slack)
+    static __host__ __device__ constexpr size_t bytes(int cap) { return size_t(cap + 2) * 8 + size_t(cap + 4) * 4 + size_t(RP) * 4; }
+};
+
+template <int K, int BLOCK, int UR, bool REGGRAM>
+__global__ void __launch_bounds__(BLOCK, REGGRAM ? 2 : 3) spmm_csr_tile_kernel(CsrView<double> A, BlockArgs<double> ba, int cap) {
     static_assert(K == 4 || K == 8, "tile kernel: K = 4 or 8");
+    static_assert(!REGGRAM || K == 4, "register Gram sums: K = 4 only");
     constexpr int LPR = K / 4;          // lanes per row
     constexpr int RPP = BLOCK / LPR;    // rows per CTA pass
-    constexpr int UR = 256;             // rows per unit (staged together)
     constexpr int PASSES = UR / RPP;
-    constexpr int CAP = 2048;           // staged entries per unit; a unit with more reads the matrix from global
+    static_assert(PASSES >= 1 && UR % RPP == 0, "unit = whole passes");
     constexpr int RW = 32 / LPR;        // rows per warp pass
-    constexpr int TW = 2 * K;           // tile row: q[0..K) then v[0..K)
+    constexpr int TW = 8;               // K = 8 tile row (one tile for q, one for v)
+    constexpr int NT = K / 4;           // tiles per warp
+    // K = 4: four planes of 32 x double2 -- (q0,q1) (q2,q3) (v0,v1) (v2,v3) -- 576 bytes apart: a lane's 16-byte
+    // stores are consecutive across the warp and the fragment loads of a half warp fall in disjoint banks
+    constexpr int PL = 72;
     constexpr int NE = BlockSums<K>::NE, NC = BlockSums<K>::NC;
+    extern __shared__ __align__(128) unsigned char stage_smem[];
+    __shared__ __align__(8) unsigned long long bar[2];
+    __shared__ int meta[2][4];  // e0a (first staged value), e0c (first staged column), staged?, rows
     __shared__ double sT[K * K];
-    __shared__ double sval[CAP];
-    __shared__ int scol[CAP];
-    __shared__ int srp[UR + 1];
-    __shared__ __align__(16) double tile[BLOCK / 32][RW * TW];
+    __shared__ __align__(16) double tile[REGGRAM ? 1 : BLOCK / 32][NT][K == 4 ? 4 * PL : RW * TW];
     __shared__ double sred[BLOCK / 32][NE];
     const BlockState* st = ba.st;
     if (st->stop != BSTOP_NONE) return;
@@ -348,66 +400,107 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_tile_kernel(CsrView<double> A,
     const double* __restrict__ U = ba.u[L & 1];
     double* __restrict__ out = ba.u[(L + 1) & 1];
     load_T<double, K>(st, L, sT);
+    const size_t sbytes = TileStage<UR>::bytes(cap);
+    auto stage_val = [&](int s) { return reinterpret_cast<double*>(stage_smem + s * sbytes); };
+    auto stage_col = [&](int s) { return reinterpret_cast<int*>(stage_smem + s * sbytes + size_t(cap + 2) * 8); };
+    auto stage_rp = [&](int s) { return reinterpret_cast<int*>(stage_smem + s * sbytes + size_t(cap + 2) * 8 + size_t(cap + 4) * 4); };
+    const int nunits = (A.rows + UR - 1) / UR;
+    // one thread: start the copies of `unit` into stage s
+    auto issue = [&](int unit, int s) {
+        const int r0 = unit * UR, nr = min(UR, A.rows - r0);
+        const int e0 = __ldg(A.rowptr + r0), e1 = __ldg(A.rowptr + r0 + nr);
+        const int e0a = e0 & ~1, e0c = e0 & ~3;
+        const bool fits = e1 - e0 <= cap;
+        meta[s][0] = e0a;
+        meta[s][1] = e0c;
+        meta[s][2] = fits ? 1 : 0;
+        meta[s][3] = nr;
+        const unsigned brp = unsigned((nr + 1) * 4 + 15) & ~15u;
+        const unsigned bv = fits ? unsigned((e1 - e0a) * 8 + 15) & ~15u : 0u;
+        const unsigned bc = fits ? unsigned((e1 - e0c) * 4 + 15) & ~15u : 0u;
+        mbar_expect(&bar[s], brp + bv + bc);
+        tma_copy_1d(stage_rp(s), A.rowptr + r0, brp, &bar[s]);
+        if (bv) tma_copy_1d(stage_val(s), A.vals + e0a, bv, &bar[s]);
+        if (bc) tma_copy_1d(stage_col(s), A.colidx + e0c, bc, &bar[s]);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        const int first = block_unit_at(0, ba.chunk, nunits);
+        if (first >= 0) issue(first, 0);
+    }
+    __syncthreads();  // barriers initialised, sT loaded
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = threadIdx.x % LPR;        // which 4 columns of the row this lane owns
     const int fr = lane & 3, fc = lane >> 2;  // mma fragment coordinates
-    double* wt = tile[warp];
-    // accumulators: K = 8: (c0, c1) = C fragment, (w0, w1) = W fragment; K = 4: (c0, c1) = the stacked 8 x 8 tile
+    // (c0, c1): K = 8: C fragment; K = 4: the stacked tile [Q^T V ; V^T V | ...].  (w0, w1): K = 8: W fragment.
     double c0 = 0.0, c1 = 0.0, w0 = 0.0, w1 = 0.0;
-    const int nunits = (A.rows + UR - 1) / UR;
-    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
-        const int r0 = unit * UR, nr = min(UR, A.rows - r0);
-        __syncthreads();  // the previous unit's readers are done with the staged arrays
-        for (int i = threadIdx.x; i <= nr; i += BLOCK) srp[i] = __ldg(A.rowptr + r0 + i);
-        __syncthreads();
-        const int e0 = srp[0], ne = srp[nr] - e0;
-        const bool staged = ne <= CAP;
-        if (staged)
-            for (int i = threadIdx.x; i < ne; i += BLOCK) {
-                sval[i] = ld_stream_f64(A.vals + e0 + i);
-                scol[i] = ld_stream_s32(A.colidx + e0 + i);
-            }
-        __syncthreads();
+    BlockAcc<double, 4> acc4;  // REGGRAM: the 26 sums of a thread's rows in registers
+    acc4.clear();
+    double treg[10];  // K = 4: the upper triangle of T in registers
+    if constexpr (K == 4) {
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = a; b < 4; ++b) treg[a * 4 - a * (a - 1) / 2 + (b - a)] = sT[a * 4 + b];
+    }
+    for (int it = 0, unit; (unit = block_unit_at(it, ba.chunk, nunits)) >= 0; ++it) {
+        const int s = it & 1;
+        if (threadIdx.x == 0) {
+            const int next = block_unit_at(it + 1, ba.chunk, nunits);
+            if (next >= 0) issue(next, s ^ 1);
+        }
+        mbar_wait_bounded(&bar[s], unsigned(it >> 1) & 1u);
+        const int e0a = meta[s][0], e0c = meta[s][1], nr = meta[s][3];
+        const bool staged = meta[s][2] != 0;
+        const double* __restrict__ sval = stage_val(s);
+        const int* __restrict__ scol = stage_col(s);
+        const int* __restrict__ srp = stage_rp(s);
+        const int r0 = unit * UR;
 #pragma unroll 1
         for (int pass = 0; pass < PASSES; ++pass) {
             const int lr = pass * RPP + threadIdx.x / LPR, row = r0 + lr;
             const bool valid = lr < nr;
             double y[4] = {0.0, 0.0, 0.0, 0.0}, own[4] = {0.0, 0.0, 0.0, 0.0};
             if (valid) {
-                const int p0 = srp[lr] - e0, p1 = srp[lr + 1] - e0;
-                int p = p0;
-                for (; p + 1 < p1; p += 2) {  // two gathers in flight
-                    const int ca = staged ? scol[p] : __ldg(A.colidx + e0 + p);
-                    const int cb = staged ? scol[p + 1] : __ldg(A.colidx + e0 + p + 1);
-                    const double va = staged ? sval[p] : __ldg(A.vals + e0 + p);
-                    const double vb = staged ? sval[p + 1] : __ldg(A.vals + e0 + p + 1);
-                    double ua[4], ub[4];
-                    ld_nc_f64x4(U + int64_t(ca) * K + 4 * sub, ua);
-                    ld_nc_f64x4(U + int64_t(cb) * K + 4 * sub, ub);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) y[j] = fma(va, ua[j], y[j]);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) y[j] = fma(vb, ub[j], y[j]);
-                }
-                if (p < p1) {
-                    const int ca = staged ? scol[p] : __ldg(A.colidx + e0 + p);
-                    const double va = staged ? sval[p] : __ldg(A.vals + e0 + p);
-                    double ua[4];
-                    ld_nc_f64x4(U + int64_t(ca) * K + 4 * sub, ua);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) y[j] = fma(va, ua[j], y[j]);
-                }
+                const int p0 = srp[lr], p1 = srp[lr + 1];
                 ld_nc_f64x4(U + int64_t(row) * K + 4 * sub, own);
-            }
-            // the whole row of y and own in every lane of the row's lane group
-            double yf[K], of[K];
-            if constexpr (LPR == 1) {
+                for (int p = p0; p < p1; p += 4) {  // four gathers in flight
+                    int col[4];
+                    double a[4], u[4][4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    yf[j] = y[j];
-                    of[j] = own[j];
+                    for (int i = 0; i < 4; ++i) {
+                        const bool ok = p + i < p1;
+                        const int pp = ok ? p + i : p;
+                        col[i] = staged ? scol[pp - e0c] : __ldg(A.colidx + pp);
+                        a[i] = staged ? sval[pp - e0a] : __ldg(A.vals + pp);
+                        if (!ok) a[i] = 0.0;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) ld_nc_f64x4(U + int64_t(col[i]) * K + 4 * sub, u[i]);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) y[j] = fma(a[i], u[i][j], y[j]);
+                }
+            }
+            double v[4], q[4];
+            if constexpr (K == 4) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    double vv = 0.0, qq = 0.0;
+#pragma unroll
+                    for (int a = 0; a <= b; ++a) {
+                        const double t = treg[a * 4 - a * (a - 1) / 2 + (b - a)];
+                        vv = fma(y[a], t, vv);
+                        qq = fma(own[a], t, qq);
+                    }
+                    v[b] = vv * sigma;
+                    q[b] = qq;
                 }
             } else {
+                // the whole row of y and own in both lanes of the row
+                double yf[K], of[K];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const double yo = __shfl_xor_sync(0xffffffffu, y[j], 1), oo = __shfl_xor_sync(0xffffffffu, own[j], 1);
@@ -416,41 +509,70 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_tile_kernel(CsrView<double> A,
                     of[j] = sub == 0 ? own[j] : oo;
                     of[4 + j] = sub == 0 ? oo : own[j];
                 }
-            }
-            double v[4], q[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                double vv = 0.0, qq = 0.0;
+                for (int j = 0; j < 4; ++j) {
+                    double vv = 0.0, qq = 0.0;
 #pragma unroll
-                for (int a = 0; a < K; ++a) {
-                    const double t = sT[a * K + 4 * sub + j];  // zero below the diagonal
-                    vv = fma(yf[a], t, vv);
-                    qq = fma(of[a], t, qq);
+                    for (int a = 0; a < K; ++a) {
+                        const double t = sT[a * K + 4 * sub + j];  // zero below the diagonal
+                        vv = fma(yf[a], t, vv);
+                        qq = fma(of[a], t, qq);
+                    }
+                    v[j] = vv * sigma;
+                    q[j] = qq;
                 }
-                v[j] = vv * sigma;
-                q[j] = qq;
             }
             if (valid) st_f64x4(out + int64_t(row) * K + 4 * sub, v);
-            // q and v of the warp's RW rows into its tile (zeros for rows past the end), then the Gram updates
-            double* tr = wt + (lane / LPR) * TW;
-            *reinterpret_cast<double4*>(tr + 4 * sub) = make_double4(q[0], q[1], q[2], q[3]);
-            *reinterpret_cast<double4*>(tr + K + 4 * sub) = make_double4(v[0], v[1], v[2], v[3]);
-            __syncwarp();
+            // q and v of the warp's rows into its tile(s) (zeros for rows past the end), then the Gram updates
+            // on the fp64 tensor cores: every 4 rows are one (K = 4) or two (K = 8) mma.m8n8k4
+            if constexpr (REGGRAM) {
 #pragma unroll
-            for (int j = 0; j < RW / 4; ++j) {
-                const double* r4 = wt + (4 * j + fr) * TW;
-                if constexpr (K == 8) {
-                    const double qa = r4[fc], vb = r4[K + fc];
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) acc4.c[a * 4 + b] = fma(q[a], v[b], acc4.c[a * 4 + b]);
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = a; b < 4; ++b) {
+                        const int e = a * 4 - a * (a - 1) / 2 + (b - a);
+                        acc4.w[e] = fma(v[a], v[b], acc4.w[e]);
+                    }
+            } else if constexpr (K == 4) {
+                double2* tp = reinterpret_cast<double2*>(tile[warp][0]);
+                tp[lane] = make_double2(q[0], q[1]);
+                tp[PL / 2 + lane] = make_double2(q[2], q[3]);
+                tp[2 * (PL / 2) + lane] = make_double2(v[0], v[1]);
+                tp[3 * (PL / 2) + lane] = make_double2(v[2], v[3]);
+                __syncwarp();
+                const double* tw = tile[warp][0];
+                const int ca = fc, cb = (fc + 4) & 7;  // A rows: q_0..q_3, v_0..v_3; B columns: v_0..v_3, q_0..q_3
+                const double* pa = tw + (ca >> 1) * PL + (ca & 1) + 2 * fr;
+                const double* pb = tw + (cb >> 1) * PL + (cb & 1) + 2 * fr;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) dmma_8x8x4(c0, c1, pa[8 * j], pb[8 * j]);  // rows 4j + fr
+                __syncwarp();
+            } else {
+                double* tq = tile[warp][0] + (lane / LPR) * TW + 4 * sub;
+                double* tv = tile[warp][1] + (lane / LPR) * TW + 4 * sub;
+                *reinterpret_cast<double2*>(tq) = make_double2(q[0], q[1]);
+                *reinterpret_cast<double2*>(tq + 2) = make_double2(q[2], q[3]);
+                *reinterpret_cast<double2*>(tv) = make_double2(v[0], v[1]);
+                *reinterpret_cast<double2*>(tv + 2) = make_double2(v[2], v[3]);
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < RW / 4; ++j) {
+                    const double qa = tile[warp][0][(4 * j + fr) * TW + fc], vb = tile[warp][1][(4 * j + fr) * TW + fc];
                     dmma_8x8x4(c0, c1, qa, vb);  // C += Q^T V
                     dmma_8x8x4(w0, w1, vb, vb);  // W += V^T V
-                } else {
-                    const double a8 = r4[fc];            // rows of A: q_0..q_3, v_0..v_3
-                    const double b8 = r4[(fc + 4) & 7];  // columns of B: v_0..v_3, q_0..q_3
-                    dmma_8x8x4(c0, c1, a8, b8);          // top-left 4 x 4 = Q^T V, bottom-left = V^T V
                 }
+                __syncwarp();
             }
-            __syncwarp();
         }
+        __syncthreads();  // everyone is done with stage s before the copies of unit + 2 * grid land in it
+    }
+    if constexpr (REGGRAM) {
+        block_cta_reduce<double, 4, BLOCK>(acc4, ba.partials, ba.nslots, blockIdx.x);
+        return;
     }
     // fragments -> entries.  Lane holds D[fc][2 fr], D[fc][2 fr + 1].
     for (int i = lane; i < NE; i += 32) sred[warp][i] = 0.0;
@@ -462,18 +584,16 @@ __global__ void __launch_bounds__(BLOCK) spmm_csr_tile_kernel(CsrView<double> A,
             sred[warp][a * K + b] = h ? c1 : c0;
             if (a <= b) sred[warp][NC + a * K - a * (a - 1) / 2 + (b - a)] = h ? w1 : w0;
         }
-    } else {
-        if (fr < 2) {
+    } else if (fr < 2) {
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int b = 2 * fr + h;
-                const double d = h ? c1 : c0;
-                if (fc < 4) {
-                    sred[warp][fc * K + b] = d;
-                } else {
-                    const int a = fc - 4;
-                    if (a <= b) sred[warp][NC + a * K - a * (a - 1) / 2 + (b - a)] = d;
-                }
+        for (int h = 0; h < 2; ++h) {
+            const int b = 2 * fr + h;
+            const double d = h ? c1 : c0;
+            if (fc < 4) {
+                sred[warp][fc * K + b] = d;
+            } else if (fc - 4 <= b) {
+                const int a = fc - 4;
+                sred[warp][NC + a * K - a * (a - 1) / 2 + (b - a)] = d;
             }
         }
     }
@@ -595,6 +715,9 @@ template <int BLOCK>
 __global__ void __launch_bounds__(BLOCK) block_control_kernel(BlockState* st, const double* __restrict__ partials, int nslots,
                                                               int k, int is_complex, int begin) {
     __shared__ double tot[2 * (kBlockElems + kBlockMax * (kBlockMax + 1) / 2)];
+    __shared__ Cx sC[kBlockElems], sW[kBlockElems], sH[kBlockElems], swork[kBlockElems];
+    __shared__ Cx stheta[kBlockMax];
+    __shared__ int flags[2];  // eigenvalues ok, Cholesky ok
     if (!begin && st->stop != BSTOP_NONE) return;
     const int nc = k * k, ne = nc + k * (k + 1) / 2, stride = (is_complex ? 2 : 1) * ne;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -605,21 +728,36 @@ __global__ void __launch_bounds__(BLOCK) block_control_kernel(BlockState* st, co
         if (lane == 0) tot[i] = s;
     }
     __syncthreads();
-    if (threadIdx.x != 0) return;
-    Cx C[kBlockElems], W[kBlockElems];
-    for (int a = 0; a < k; ++a)
-        for (int b = 0; b < k; ++b) {
-            const int e = a * k + b;
-            C[a * kBlockLd + b] = cx(tot[e], is_complex ? tot[ne + e] : 0.0);
-            if (b >= a) {
-                const int ew = nc + a * k - a * (a - 1) / 2 + (b - a);
-                W[a * kBlockLd + b] = cx(tot[ew], is_complex ? tot[ne + ew] : 0.0);
-            } else {
-                W[a * kBlockLd + b] = cx(0.0);
-            }
+    for (int e = threadIdx.x; e < nc; e += BLOCK) {
+        const int a = e / k, b = e % k;
+        sC[a * kBlockLd + b] = cx(tot[e], is_complex ? tot[ne + e] : 0.0);
+        if (b >= a) {
+            const int ew = nc + a * k - a * (a - 1) / 2 + (b - a);
+            sW[a * kBlockLd + b] = cx(tot[ew], is_complex ? tot[ne + ew] : 0.0);
+        } else {
+            sW[a * kBlockLd + b] = cx(0.0);
         }
-    if (begin) block_control_begin(st, W);
-    else block_control_step(st, C, W);
+    }
+    __syncthreads();
+    if (begin) {
+        if (threadIdx.x == 0) block_control_begin(st, sW);
+        return;
+    }
+    // the three pieces of the step (blockmath.hpp): warp 0 the Ritz values, warp 1 the Cholesky factor, then thread 0
+    if (warp == 0) {
+        block_step_H(st, sC, sH, lane, 32);
+        __syncwarp();
+        Cx theta[kBlockMax];
+        const bool ok = eig_values_coop(sH, k, theta, swork, lane, 32);
+        if (lane == 0) {
+            flags[0] = ok ? 1 : 0;
+            for (int i = 0; i < k; ++i) stheta[i] = theta[i];
+        }
+    } else if (threadIdx.x == 32) {
+        flags[1] = block_step_T(st, sW) ? 1 : 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) block_step_decide(st, sH, stheta, flags[0] != 0, flags[1] != 0);
 }
 
 // ---- layout changes at the API boundary (Eigen holds n x k column-major) ---------------------------------

@@ -30,6 +30,9 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
     // launch geometry
     int grid, ntiles = 1, nseg = 1, grid_partial = 0;
     void (*spmm)(CsrView<S>, BlockArgs<S>) = nullptr;
+    void (*spmm_tile)(CsrView<double>, BlockArgs<double>, int) = nullptr;  // real K >= 4: TMA-staged tile kernel
+    int tile_cap = 0;
+    size_t tile_smem = 0;
     if (m.dense) {
         grid = int(std::min<int64_t>((n + B - 1) / B, int64_t(m.sm_count) * occupancy(block_combine_kernel<S, K, B>, B)));
         const int rt = B * DenseRpt<S>::value;
@@ -53,17 +56,35 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
         if (variant == V_ROW && !can_row) variant = V_LANES;
         const int unroll = env_int("EIGSOL_B200_BLOCK_UNROLL", 4);
         int rows_per_unit = B;
+        int occ = 1;
         if (variant == V_TILE) {
-            if constexpr (can_tile) spmm = spmm_csr_tile_kernel<K, B>;
-            rows_per_unit = 256;
+            if constexpr (can_tile) {
+                constexpr int UR = K == 4 ? 256 : 128;  // rows staged together (one CTA pass)
+                if constexpr (K == 4) {
+                    spmm_tile = env_int("EIGSOL_B200_BLOCK_REGGRAM", 0) ? spmm_csr_tile_kernel<K, B, UR, true>
+                                                                      : spmm_csr_tile_kernel<K, B, UR, false>;
+                } else {
+                    spmm_tile = spmm_csr_tile_kernel<K, B, UR, false>;
+                }
+                rows_per_unit = UR;
+                // staged entries per unit: the mean unit plus 12.5 %; a unit with more reads the matrix from global
+                const double mean_row = n > 0 ? double(m.local_nnz) / double(n) : 0.0;
+                int64_t cap = int64_t(double(UR) * mean_row * 1.125) + 32;
+                cap = std::min<int64_t>(std::max<int64_t>(cap, 256), 6144);
+                tile_cap = env_int("EIGSOL_B200_BLOCK_CAP", int((cap + 3) / 4 * 4)) / 4 * 4;
+                tile_smem = 2 * TileStage<UR>::bytes(tile_cap);
+                EIGSOL_CUDA(cudaFuncSetAttribute(spmm_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, int(tile_smem)));
+                occ = occupancy(spmm_tile, B, tile_smem);
+            }
         } else if (variant == V_LANES) {
             spmm = unroll >= 8 ? spmm_csr_lanes_kernel<S, K, B, 8>
                                : (unroll <= 2 ? spmm_csr_lanes_kernel<S, K, B, 2> : spmm_csr_lanes_kernel<S, K, B, 4>);
             rows_per_unit = B / K;
+            occ = occupancy(spmm, B);
         } else {
             if constexpr (can_row) spmm = spmm_csr_block_kernel<S, K, B>;
+            occ = occupancy(spmm, B);
         }
-        const int occ = occupancy(spmm, B);
         grid = int(std::min<int64_t>((n + rows_per_unit - 1) / rows_per_unit, int64_t(m.sm_count) * occ));
     }
     grid = std::max(grid, 1);
@@ -76,6 +97,7 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
     ba.st = d_state.as<BlockState>();
     ba.partials = d_partials.as<double>();
     ba.nslots = grid;
+    ba.chunk = std::max(1, env_int("EIGSOL_B200_BLOCK_CHUNK", 1));
 
     // start block: column-major n x K from the caller -> row-major U_0, W_0 = U_0^H U_0, T_0
     EIGSOL_CUDA(cudaMemcpyAsync(d_xcol.p, x0, size_t(n) * K * s, cudaMemcpyHostToDevice, st));
@@ -102,7 +124,12 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
             res.launches += 3;
         } else {
             CsrView<S> A{int32_t(n), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
-            spmm<<<grid, B, 0, st>>>(A, ba);
+            if constexpr (!Sc<S>::is_complex) {
+                if (spmm_tile) spmm_tile<<<grid, B, tile_smem, st>>>(A, ba, tile_cap);
+                else spmm<<<grid, B, 0, st>>>(A, ba);
+            } else {
+                spmm<<<grid, B, 0, st>>>(A, ba);
+            }
             res.launches += 2;
         }
         block_control_kernel<1024><<<1, 1024, 0, st>>>(ba.st, ba.partials, grid, K, Sc<S>::is_complex ? 1 : 0, 0);
@@ -138,6 +165,7 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
     if (!x_out) return;
     // X = U_f T_f S: the Ritz vectors of the last folded launch (power_method.hpp:98 returns x of the last trip)
     Cx M[kBlockElems];
+    block_result_vectors(hs);  // S: the loop itself only needs the Ritz values
     block_result_transform(hs, M);
     BlockMat<S, K> bm;
     if constexpr (Sc<S>::is_complex) {

@@ -55,8 +55,16 @@ EB_HD Cx operator/(Cx a, Cx b) {  // Smith's algorithm: no overflow in |b|^2
     const double r = b.re / b.im, d = b.re * r + b.im;
     return cx((a.re * r + a.im) / d, (a.im * r - a.re) / d);
 }
+// Cheap forms for data already scaled to O(1) (eig_general divides H by its largest entry first): no hypot,
+// one real division per complex division.  On the device these run in ONE thread between two launches.
+EB_HD double cabs_fast(Cx a) { return sqrt(a.re * a.re + a.im * a.im); }
+EB_HD double cabs1(Cx a) { return fabs(a.re) + fabs(a.im); }
+EB_HD Cx cdiv_fast(Cx a, Cx b) {
+    const double inv = 1.0 / (b.re * b.re + b.im * b.im);
+    return cx((a.re * b.re + a.im * b.im) * inv, (a.im * b.re - a.re * b.im) * inv);
+}
 EB_HD Cx csqrt_(Cx a) {  // principal square root
-    const double m = cabs(a);
+    const double m = cabs_fast(a);
     if (m == 0.0) return cx(0.0, 0.0);
     const double s = sqrt(0.5 * (m + fabs(a.re)));
     const double t = 0.5 * a.im / s;
@@ -102,23 +110,24 @@ EB_HDN void tri_inverse_upper(const Cx* R, int k, Cx* T) {
 // ---- complex Schur decomposition of a small general matrix -------------------------------------------
 // Rotation G = [c s; -conj(s) c] (c real) with G [a; b] = [r; 0].
 EB_HD void givens(Cx a, Cx b, double& c, Cx& s) {
-    const double nb = cabs(b);
-    if (nb == 0.0) {
+    const double nb2 = cabs2(b);
+    if (nb2 == 0.0) {
         c = 1.0;
         s = cx(0.0);
         return;
     }
-    const double na = cabs(a);
-    if (na == 0.0) {
+    const double na2 = cabs2(a);
+    if (na2 == 0.0) {
+        const double inv = 1.0 / sqrt(nb2);
         c = 0.0;
-        s = cx(b.re / nb, -b.im / nb);
+        s = cx(b.re * inv, -b.im * inv);
         return;
     }
-    const double nrm = hypot(na, nb);
-    c = na / nrm;
-    const Cx ph = cx(a.re / na, a.im / na);
-    s = ph * conj(b);
-    s = cx(s.re / nrm, s.im / nrm);
+    const double na = sqrt(na2), inv_nrm = 1.0 / sqrt(na2 + nb2);
+    c = na * inv_nrm;
+    const double f = inv_nrm / na;  // s = (a / |a|) conj(b) / nrm
+    const Cx ab = a * conj(b);
+    s = cx(ab.re * f, ab.im * f);
 }
 // rows (i, j) of M <- G * rows, columns q0..k-1
 EB_HD void rot_rows(Cx* M, int k, int i, int j, double c, Cx s, int q0) {
@@ -139,39 +148,68 @@ EB_HD void rot_cols(Cx* M, int i, int j, double c, Cx s, int p1) {
 
 // In place: M (general k x k) -> upper triangular Tm, Z unitary with M_in = Z Tm Z^H.  Returns false if
 // the QR iteration did not converge (60 sweeps on one eigenvalue).
-EB_HDN bool schur_complex(Cx* M, int k, Cx* Z) {
-    for (int i = 0; i < k; ++i)
-        for (int j = 0; j < k; ++j) Z[i * kBlockLd + j] = cx(i == j ? 1.0 : 0.0);
+//
+// Written for `nl` cooperating lanes (lane = 0..nl-1) that share M and Z and step together: every lane
+// evaluates the (identical) scalar decisions and rotation coefficients, and applies a rotation to its own
+// columns / rows; EB_SYNC() separates the phases.  On the device the lanes are the 32 threads of one warp
+// and M, Z live in shared memory; the host runs the same code with nl = 1.  Element by element the arithmetic
+// is the same for every nl, so the host run is a bit-exact model of the device run.
+// Z == nullptr: eigenvalues only -- rotations are then confined to the active window [l, hi].
+#if defined(__CUDA_ARCH__)
+#define EB_SYNC() __syncwarp()
+#else
+#define EB_SYNC() ((void)0)
+#endif
+
+EB_HDN bool schur_coop(Cx* M, int k, Cx* Z, int lane, int nl) {
+    if (Z)
+        for (int e = lane; e < k * k; e += nl) Z[(e / k) * kBlockLd + e % k] = cx(e / k == e % k ? 1.0 : 0.0);
+    EB_SYNC();
     // Hessenberg form by Givens similarity transforms
     for (int j = 0; j + 2 < k; ++j)
         for (int i = k - 1; i >= j + 2; --i) {
-            if (cabs(M[i * kBlockLd + j]) == 0.0) continue;
+            const Cx a = M[(i - 1) * kBlockLd + j], b = M[i * kBlockLd + j];
+            EB_SYNC();  // everyone has read the pivot pair
+            if (cabs1(b) == 0.0) continue;
             double c;
             Cx s;
-            givens(M[(i - 1) * kBlockLd + j], M[i * kBlockLd + j], c, s);
-            rot_rows(M, k, i - 1, i, c, s, j);
-            M[i * kBlockLd + j] = cx(0.0);
-            rot_cols(M, i - 1, i, c, s, k);
-            rot_cols(Z, i - 1, i, c, s, k);
+            givens(a, b, c, s);
+            for (int q = j + lane; q < k; q += nl) {  // rows (i-1, i) <- G rows
+                const Cx x = M[(i - 1) * kBlockLd + q], y = M[i * kBlockLd + q];
+                M[(i - 1) * kBlockLd + q] = c * x + s * y;
+                M[i * kBlockLd + q] = q == j ? cx(0.0) : c * y - conj(s) * x;
+            }
+            EB_SYNC();
+            for (int p = lane; p < k; p += nl) {  // columns (i-1, i) <- columns G^H
+                const Cx x = M[p * kBlockLd + i - 1], y = M[p * kBlockLd + i];
+                M[p * kBlockLd + i - 1] = c * x + conj(s) * y;
+                M[p * kBlockLd + i] = c * y - s * x;
+                if (Z) {
+                    const Cx zx = Z[p * kBlockLd + i - 1], zy = Z[p * kBlockLd + i];
+                    Z[p * kBlockLd + i - 1] = c * zx + conj(s) * zy;
+                    Z[p * kBlockLd + i] = c * zy - s * zx;
+                }
+            }
+            EB_SYNC();
         }
     const double eps = 2.220446049250313e-16;
     double norm = 0.0;
     for (int i = 0; i < k; ++i)
-        for (int j = 0; j < k; ++j) norm = fmax(norm, cabs(M[i * kBlockLd + j]));
+        for (int j = 0; j < k; ++j) norm = fmax(norm, cabs1(M[i * kBlockLd + j]));
     int hi = k - 1, sweeps = 0;
     double cs[kBlockMax];
     Cx sn[kBlockMax];
     while (hi > 0) {
         int l = hi;
         for (; l > 0; --l) {
-            const double sub = cabs(M[l * kBlockLd + l - 1]);
-            double diag = cabs(M[(l - 1) * kBlockLd + l - 1]) + cabs(M[l * kBlockLd + l]);
+            const double sub = cabs1(M[l * kBlockLd + l - 1]);  // |re| + |im|, as LAPACK's zlahqr deflation test
+            double diag = cabs1(M[(l - 1) * kBlockLd + l - 1]) + cabs1(M[l * kBlockLd + l]);
             if (diag == 0.0) diag = norm;
-            if (sub <= eps * diag) {
-                M[l * kBlockLd + l - 1] = cx(0.0);
-                break;
-            }
+            if (sub <= eps * diag) break;
         }
+        EB_SYNC();
+        if (l > 0 && lane == 0) M[l * kBlockLd + l - 1] = cx(0.0);
+        EB_SYNC();
         if (l == hi) {  // M[hi][hi] is an eigenvalue
             --hi;
             sweeps = 0;
@@ -181,36 +219,61 @@ EB_HDN bool schur_complex(Cx* M, int k, Cx* Z) {
         // Wilkinson shift: the eigenvalue of the trailing 2 x 2 nearer to its last diagonal entry
         const Cx a = M[(hi - 1) * kBlockLd + hi - 1], b = M[(hi - 1) * kBlockLd + hi];
         const Cx c2 = M[hi * kBlockLd + hi - 1], d = M[hi * kBlockLd + hi];
+        const double below = hi >= 2 ? cabs1(M[(hi - 1) * kBlockLd + hi - 2]) : 0.0;
+        EB_SYNC();
         Cx mu;
         if (sweeps == 10 || sweeps == 20 || sweeps == 30) {
-            mu = cx(cabs(c2) + (hi >= 2 ? cabs(M[(hi - 1) * kBlockLd + hi - 2]) : 0.0)) + d;  // exceptional shift
+            mu = cx(cabs1(c2) + below) + d;  // exceptional shift
         } else {
             const Cx half = 0.5 * (a - d);
             const Cx disc = csqrt_(half * half + b * c2);
             const Cx m1 = 0.5 * (a + d) + disc, m2 = 0.5 * (a + d) - disc;
-            mu = cabs(m1 - d) <= cabs(m2 - d) ? m1 : m2;
+            mu = cabs2(m1 - d) <= cabs2(m2 - d) ? m1 : m2;
         }
-        for (int i = l; i <= hi; ++i) M[i * kBlockLd + i] = M[i * kBlockLd + i] - mu;
-        for (int i = l; i < hi; ++i) {  // M - mu = Q R
-            givens(M[i * kBlockLd + i], M[(i + 1) * kBlockLd + i], cs[i], sn[i]);
-            rot_rows(M, k, i, i + 1, cs[i], sn[i], i);
-            M[(i + 1) * kBlockLd + i] = cx(0.0);
+        for (int i = l + lane; i <= hi; i += nl) M[i * kBlockLd + i] = M[i * kBlockLd + i] - mu;
+        EB_SYNC();
+        const int qend = Z ? k : hi + 1;  // eigenvalues only: stay inside the window
+        for (int i = l; i < hi; ++i) {    // M - mu = Q R
+            const Cx pa = M[i * kBlockLd + i], pb = M[(i + 1) * kBlockLd + i];
+            EB_SYNC();
+            givens(pa, pb, cs[i], sn[i]);
+            for (int q = i + lane; q < qend; q += nl) {
+                const Cx x = M[i * kBlockLd + q], y = M[(i + 1) * kBlockLd + q];
+                M[i * kBlockLd + q] = cs[i] * x + sn[i] * y;
+                M[(i + 1) * kBlockLd + q] = q == i ? cx(0.0) : cs[i] * y - conj(sn[i]) * x;
+            }
+            EB_SYNC();
         }
-        for (int i = l; i < hi; ++i) {  // R Q, and the rows above the window so the full Schur form is kept
-            rot_cols(M, i, i + 1, cs[i], sn[i], i + 2);
-            rot_cols(Z, i, i + 1, cs[i], sn[i], k);
+        const int pbeg = Z ? 0 : l;
+        for (int i = l; i < hi; ++i) {  // R Q (and, with Z, the rows above the window: the full Schur form)
+            for (int p = pbeg + lane; p < (Z ? k : i + 2); p += nl) {
+                if (p < i + 2) {
+                    const Cx x = M[p * kBlockLd + i], y = M[p * kBlockLd + i + 1];
+                    M[p * kBlockLd + i] = cs[i] * x + conj(sn[i]) * y;
+                    M[p * kBlockLd + i + 1] = cs[i] * y - sn[i] * x;
+                }
+                if (Z) {
+                    const Cx zx = Z[p * kBlockLd + i], zy = Z[p * kBlockLd + i + 1];
+                    Z[p * kBlockLd + i] = cs[i] * zx + conj(sn[i]) * zy;
+                    Z[p * kBlockLd + i + 1] = cs[i] * zy - sn[i] * zx;
+                }
+            }
+            EB_SYNC();
         }
-        for (int i = l; i <= hi; ++i) M[i * kBlockLd + i] = M[i * kBlockLd + i] + mu;
+        for (int i = l + lane; i <= hi; i += nl) M[i * kBlockLd + i] = M[i * kBlockLd + i] + mu;
+        EB_SYNC();
     }
-    for (int i = 1; i < k; ++i)
-        for (int j = 0; j < i; ++j) M[i * kBlockLd + j] = cx(0.0);
+    for (int e = lane; e < k * k; e += nl)
+        if (e / k > e % k) M[(e / k) * kBlockLd + e % k] = cx(0.0);
+    EB_SYNC();
     return true;
 }
+EB_HDN bool schur_complex(Cx* M, int k, Cx* Z) { return schur_coop(M, k, Z, 0, 1); }
 
 // Order of the Ritz values: larger modulus first; moduli equal to 1e-9 relative (conjugate pairs, multiple
 // eigenvalues) are ordered by imaginary part, then real part, so the order is stable from trip to trip.
 EB_HD bool ritz_before(Cx a, Cx b) {
-    const double ma = cabs(a), mb = cabs(b), sc = fmax(ma, mb);
+    const double ma = cabs_fast(a), mb = cabs_fast(b), sc = fmax(ma, mb);  // called on the scaled matrix
     const double tie = 1e-9 * sc;
     if (fabs(ma - mb) > tie) return ma > mb;
     if (fabs(a.im - b.im) > tie) return a.im > b.im;
@@ -218,16 +281,69 @@ EB_HD bool ritz_before(Cx a, Cx b) {
     return false;
 }
 
+// 2^e ~ max|h_ij| (e clamped): the Schur iteration runs on H * 2^-e, exactly representable.
+EB_HD bool eig_scale(const Cx* H, int k, double& hs, double& hback) {
+    double hmax = 0.0;
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) hmax = fmax(hmax, fmax(fabs(H[i * kBlockLd + j].re), fabs(H[i * kBlockLd + j].im)));
+    if (!(hmax < HUGE_VAL)) return false;  // inf / NaN
+    int he = 0;
+    if (hmax > 0.0) frexp(hmax, &he);
+    he = he < -1000 ? -1000 : (he > 1000 ? 1000 : he);
+    hs = ldexp(1.0, -he);
+    hback = ldexp(1.0, he);
+    return true;
+}
+// ord[c] = index of the c-th diagonal entry of the triangular M in ritz_before order (insertion sort, stable)
+EB_HD void ritz_order(const Cx* M, int k, int* ord) {
+    for (int i = 0; i < k; ++i) ord[i] = i;
+    for (int i = 1; i < k; ++i) {
+        const int o = ord[i];
+        int j = i - 1;
+        while (j >= 0 && ritz_before(M[o * kBlockLd + o], M[ord[j] * kBlockLd + ord[j]])) {
+            ord[j + 1] = ord[j];
+            --j;
+        }
+        ord[j + 1] = o;
+    }
+}
+
+// The ordered eigenvalues only, by `nl` cooperating lanes (see schur_coop); `work` is a k x k scratch shared by
+// the lanes, theta is each lane's own (identical) copy.  This is what runs between two launches: the convergence
+// test needs no vectors.  The values are bit-identical to eig_general's.
+EB_HDN bool eig_values_coop(const Cx* H, int k, Cx* theta, Cx* work, int lane, int nl) {
+    double hs, hback;
+    if (!eig_scale(H, k, hs, hback)) return false;
+    for (int e = lane; e < k * k; e += nl) {
+        const int i = (e / k) * kBlockLd + e % k;
+        work[i] = cx(H[i].re * hs, H[i].im * hs);
+    }
+    EB_SYNC();
+    if (!schur_coop(work, k, nullptr, lane, nl)) return false;
+    int ord[kBlockMax];
+    ritz_order(work, k, ord);
+    for (int c = 0; c < k; ++c) {
+        const Cx d = work[ord[c] * kBlockLd + ord[c]];
+        theta[c] = cx(d.re * hback, d.im * hback);
+    }
+    EB_SYNC();
+    return true;
+}
+
 // Eigenvalues theta[0..k) (ordered by ritz_before) and unit-norm eigenvectors (columns of S, largest component
 // real and positive) of the general matrix H.  H is not modified.  false: the QR iteration failed.
 EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
     Cx M[kBlockElems], Z[kBlockElems], V[kBlockElems];
+    // work on H * 2^-e with 2^e ~ max|h_ij| (exact; the Ritz values are multiplied back at the end), so the
+    // plain sqrt / reciprocal forms above can neither overflow nor underflow
+    double hs, hback;
+    if (!eig_scale(H, k, hs, hback)) return false;
     for (int i = 0; i < k; ++i)
-        for (int j = 0; j < k; ++j) M[i * kBlockLd + j] = H[i * kBlockLd + j];
+        for (int j = 0; j < k; ++j) M[i * kBlockLd + j] = cx(H[i * kBlockLd + j].re * hs, H[i * kBlockLd + j].im * hs);
     if (!schur_complex(M, k, Z)) return false;
     double norm = 0.0;
     for (int i = 0; i < k; ++i)
-        for (int j = i; j < k; ++j) norm = fmax(norm, cabs(M[i * kBlockLd + j]));
+        for (int j = i; j < k; ++j) norm = fmax(norm, cabs1(M[i * kBlockLd + j]));
     const double small = fmax(norm * 2.220446049250313e-16, 1e-300);
     // eigenvectors of the triangular factor: column i of V
     for (int i = 0; i < k; ++i) {
@@ -238,25 +354,15 @@ EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
             Cx s = cx(0.0);
             for (int p = r + 1; p <= i; ++p) s = s + M[r * kBlockLd + p] * V[p * kBlockLd + i];
             Cx den = M[r * kBlockLd + r] - lam;
-            if (cabs(den) < small) den = cx(small);
-            V[r * kBlockLd + i] = -(s / den);
+            if (cabs1(den) < small) den = cx(small);
+            V[r * kBlockLd + i] = -cdiv_fast(s, den);
         }
     }
-    // order
     int ord[kBlockMax];
-    for (int i = 0; i < k; ++i) ord[i] = i;
-    for (int i = 1; i < k; ++i) {  // insertion sort, stable
-        const int o = ord[i];
-        int j = i - 1;
-        while (j >= 0 && ritz_before(M[o * kBlockLd + o], M[ord[j] * kBlockLd + ord[j]])) {
-            ord[j + 1] = ord[j];
-            --j;
-        }
-        ord[j + 1] = o;
-    }
+    ritz_order(M, k, ord);
     for (int c = 0; c < k; ++c) {
         const int i = ord[c];
-        theta[c] = M[i * kBlockLd + i];
+        theta[c] = cx(M[i * kBlockLd + i].re * hback, M[i * kBlockLd + i].im * hback);
         double n2 = 0.0, best = -1.0;
         Cx big = cx(1.0);
         for (int r = 0; r < k; ++r) {
@@ -270,7 +376,7 @@ EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
                 big = s;
             }
         }
-        const double nb = cabs(big);
+        const double nb = cabs_fast(big);
         const Cx ph = nb > 0.0 ? cx(big.re / nb, -big.im / nb) : cx(1.0);  // conj(big)/|big|
         const double inv = n2 > 0.0 ? 1.0 / sqrt(n2) : 1.0;
         for (int r = 0; r < k; ++r) S[r * kBlockLd + c] = inv * (ph * S[r * kBlockLd + c]);
@@ -296,8 +402,8 @@ struct BlockState {
     double sigma;     // power-of-two prescale of A (U_{m+1} = sigma A Q_m), H = C / sigma
     Cx theta[kBlockMax];        // current Ritz values, ordered
     Cx T[2][kBlockElems];       // T[L & 1] = R^{-1} used by launch L
-    Cx S[kBlockElems];          // Ritz vectors of H_{final_launch} in the Q basis
-    Cx H[kBlockElems];          // H of the last folded launch (diagnostics / tests)
+    Cx S[kBlockElems];          // Ritz vectors of H_{final_launch} in the Q basis (block_result_vectors, after the loop)
+    Cx H[kBlockElems];          // H_{final_launch}
 };
 
 EB_HD bool block_close_relative(Cx a, Cx b, double tol) {  // tolerance.hpp:28-33, a = new value
@@ -325,18 +431,34 @@ EB_HDN void block_control_begin(BlockState* st, const Cx* W) {
 
 // After SpMM launch L = st->launch_no:  C = Q_L^H (sigma A Q_L),  W = U_{L+1}^H U_{L+1}.
 // Launch 0 is the set-up product A Q_0 (the reference never forms x0^H A x0); launch L >= 1 closes trip
-// L - 1 of power_method.hpp:68-96 for every wanted Ritz value.
-EB_HDN void block_control_step(BlockState* st, const Cx* C, const Cx* W) {
-    const int k = st->k, L = st->launch_no;
+// L - 1 of power_method.hpp:68-96 for every wanted Ritz value.  The step is three independent pieces so the
+// control kernel can run them side by side:
+//     H = C / sigma and its ordered eigenvalues                       (one warp, cooperatively)
+//     W = R^H R,  T_{L+1} = R^{-1} written into st->T[(L + 1) & 1]     (another warp; harmless if the loop stops)
+//     the decision below                                              (one thread, after both)
+EB_HD void block_step_H(const BlockState* st, const Cx* C, Cx* Hn, int lane, int nl) {
     const double inv_sigma = 1.0 / st->sigma;
-    Cx theta[kBlockMax];
-    for (int i = 0; i < k; ++i)
-        for (int j = 0; j < k; ++j) st->H[i * kBlockLd + j] = inv_sigma * C[i * kBlockLd + j];
+    const int k = st->k;
+    for (int e = lane; e < k * k; e += nl) {
+        const int i = (e / k) * kBlockLd + e % k;
+        Hn[i] = inv_sigma * C[i];
+    }
+}
+EB_HDN bool block_step_T(BlockState* st, const Cx* W) {
+    Cx R[kBlockElems];
+    if (!chol_upper(W, st->k, R)) return false;  // A Q lost rank: the block counterpart of normY == 0 (power_method.hpp:73-76)
+    tri_inverse_upper(R, st->k, st->T[(st->launch_no + 1) & 1]);
+    return true;
+}
+EB_HDN void block_step_decide(BlockState* st, const Cx* Hn, const Cx* theta, bool eig_ok, bool chol_ok) {
+    const int k = st->k, L = st->launch_no;
     st->launch_no = L + 1;
-    if (!eig_general(st->H, k, theta, st->S)) {
+    if (!eig_ok) {
         st->stop = BSTOP_BREAKDOWN;
         return;
     }
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j) st->H[i * kBlockLd + j] = Hn[i * kBlockLd + j];
     st->final_launch = L;
     if (L >= 1) {
         bool all_close = st->initialized != 0;
@@ -354,12 +476,22 @@ EB_HDN void block_control_step(BlockState* st, const Cx* C, const Cx* W) {
             return;
         }
     }
-    Cx R[kBlockElems];
-    if (!chol_upper(W, k, R)) {  // A Q lost rank: the block counterpart of normY == 0 (power_method.hpp:73-76)
-        st->stop = BSTOP_BREAKDOWN;
-        return;
-    }
-    tri_inverse_upper(R, k, st->T[(L + 1) & 1]);
+    if (!chol_ok) st->stop = BSTOP_BREAKDOWN;
+}
+// The same step on one thread (the host restatement in tests/blockmath).
+EB_HDN void block_control_step(BlockState* st, const Cx* C, const Cx* W) {
+    Cx Hn[kBlockElems], work[kBlockElems], theta[kBlockMax];
+    block_step_H(st, C, Hn, 0, 1);
+    const bool eig_ok = eig_values_coop(Hn, st->k, theta, work, 0, 1);
+    const bool chol_ok = block_step_T(st, W);
+    block_step_decide(st, Hn, theta, eig_ok, chol_ok);
+}
+
+// After the loop (host): the Ritz vectors of H_{final_launch} in the Q basis.
+EB_HDN void block_result_vectors(BlockState* st) {
+    Cx theta[kBlockMax];
+    if (st->final_launch >= 0 && eig_general(st->H, st->k, theta, st->S)) return;
+    for (int i = 0; i < kBlockElems; ++i) st->S[i] = cx((i / kBlockLd) == (i % kBlockLd) ? 1.0 : 0.0);
 }
 
 // M = T S (k x k): the returned Ritz vectors are X = U M.

@@ -86,8 +86,10 @@ void bm_state(int* ints, double* theta, double* t_next, double* result_transform
         theta[2 * i + 1] = g_state.theta[i].im;
     }
     narrow(g_state.T[g_state.launch_no & 1], g_state.k, t_next);
+    BlockState fin = g_state;  // the host's end-of-loop step, on a copy
+    block_result_vectors(&fin);
     Cx M[kBlockElems];
-    block_result_transform(&g_state, M);
+    block_result_transform(&fin, M);
     narrow(M, g_state.k, result_transform);
 }
 }

@@ -43,16 +43,16 @@ def main():
     widths = [int(w) for w in os.environ.get("BLOCK_WIDTHS", "1,2,4,8").split(",")]
     x0 = es.random_block(n, max(widths), dt, seed=1)
     single_us = None
-    # BLOCK_CONFIGS="row;lanes:2;lanes:4;lanes:8" sweeps the SpMM variant (library knobs, read per solve)
+    # BLOCK_CONFIGS="row;lanes:2;tile::8" (kernel[:unroll[:chunk]]) sweeps the SpMM variant (library knobs, read per solve)
     configs = [c for c in os.environ.get("BLOCK_CONFIGS", "default").split(";") if c]
     for cfg in configs:
-      for key in ("EIGSOL_B200_BLOCK_KERNEL", "EIGSOL_B200_BLOCK_UNROLL"):
+      for key in ("EIGSOL_B200_BLOCK_KERNEL", "EIGSOL_B200_BLOCK_UNROLL", "EIGSOL_B200_BLOCK_CHUNK"):
           os.environ.pop(key, None)
-      if cfg != "default":
-          kern, _, unroll = cfg.partition(":")
-          os.environ["EIGSOL_B200_BLOCK_KERNEL"] = kern
-          if unroll:
-              os.environ["EIGSOL_B200_BLOCK_UNROLL"] = unroll
+      if cfg != "default":   # kernel[:unroll[:chunk]], empty fields keep the default
+          parts = (cfg.split(":") + ["", ""])[:3]
+          for key, val in zip(("EIGSOL_B200_BLOCK_KERNEL", "EIGSOL_B200_BLOCK_UNROLL", "EIGSOL_B200_BLOCK_CHUNK"), parts):
+              if val:
+                  os.environ[key] = val
       for k in widths:
         xk = np.asfortranarray(x0[:, :k])
         dm.block_power(xk, k, es.SolverOptions(5, -1.0), want_vectors=False)   # warm-up
