@@ -167,6 +167,7 @@ __device__ __forceinline__ void block_cta_reduce(const BlockAcc<S, K>& acc, doub
 // =================================================================================================
 template <class S, int K, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) spmm_csr_block_kernel(CsrView<S> A, BlockArgs<S> ba) {
+    pdl_prologue();
     __shared__ S sT[K * K];
     const BlockState* st = ba.st;
     if (st->stop != BSTOP_NONE) return;
@@ -254,6 +255,7 @@ __device__ __forceinline__ void block_cta_reduce_lanes(const S (&c)[K], const S 
 
 template <class S, int K, int BLOCK, int UNROLL>
 __global__ void __launch_bounds__(BLOCK) spmm_csr_lanes_kernel(CsrView<S> A, BlockArgs<S> ba) {
+    pdl_prologue();
     constexpr int RPU = BLOCK / K;  // rows per unit
     __shared__ S sT[K * K];
     const BlockState* st = ba.st;
@@ -376,6 +378,7 @@ template <int K, int BLOCK, int UR, bool REGGRAM>
 __global__ void __launch_bounds__(BLOCK, REGGRAM ? 2 : 3) spmm_csr_tile_kernel(CsrView<double> A, BlockArgs<double> ba, int cap) {
     static_assert(K == 4 || K == 8, "tile kernel: K = 4 or 8");
     static_assert(!REGGRAM || K == 4, "register Gram sums: K = 4 only");
+    pdl_prologue();  // programmatic dependent launch: resident early, reads nothing before the predecessor is complete
     constexpr int LPR = K / 4;          // lanes per row
     constexpr int RPP = BLOCK / LPR;    // rows per CTA pass
     constexpr int PASSES = UR / RPP;
@@ -635,6 +638,7 @@ template <class S, int K, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) gemm_block_partial_kernel(const S* __restrict__ a, int64_t lda, int rows, int cols,
                                                                    int ntiles, int nseg, BlockArgs<S> ba,
                                                                    S* __restrict__ partial) {
+    pdl_prologue();
     constexpr int RPT = DenseRpt<S>::value, CHUNK = 64;
     __shared__ S su[CHUNK * K];
     const BlockState* st = ba.st;
@@ -678,6 +682,7 @@ __global__ void __launch_bounds__(BLOCK) gemm_block_partial_kernel(const S* __re
 
 template <class S, int K, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) block_combine_kernel(const S* __restrict__ partial, int rows, int nseg, BlockArgs<S> ba) {
+    pdl_prologue();
     __shared__ S sT[K * K];
     const BlockState* st = ba.st;
     if (st->stop != BSTOP_NONE) return;
@@ -714,6 +719,7 @@ __global__ void __launch_bounds__(BLOCK) block_combine_kernel(const S* __restric
 template <int BLOCK>
 __global__ void __launch_bounds__(BLOCK) block_control_kernel(BlockState* st, const double* __restrict__ partials, int nslots,
                                                               int k, int is_complex, int begin) {
+    pdl_prologue();
     __shared__ double tot[2 * (kBlockElems + kBlockMax * (kBlockMax + 1) / 2)];
     __shared__ Cx sC[kBlockElems], sW[kBlockElems], sH[kBlockElems], swork[kBlockElems];
     __shared__ Cx stheta[kBlockMax];

@@ -118,21 +118,22 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
 
     auto one_trip = [&] {
         if (m.dense) {
-            gemm_block_partial_kernel<S, K, B><<<grid_partial, B, 0, st>>>(m.d_dense.as<S>(), m.lda, int(n), int(n), ntiles, nseg,
-                                                                          ba, d_dpart.as<S>());
-            block_combine_kernel<S, K, B><<<grid, B, 0, st>>>(d_dpart.as<S>(), int(n), nseg, ba);
+            launch_pdl(m.pdl, st, gemm_block_partial_kernel<S, K, B>, dim3(grid_partial), dim3(B), 0, m.d_dense.as<S>(), m.lda,
+                       int(n), int(n), ntiles, nseg, ba, d_dpart.as<S>());
+            launch_pdl(m.pdl, st, block_combine_kernel<S, K, B>, dim3(grid), dim3(B), 0, d_dpart.as<S>(), int(n), nseg, ba);
             res.launches += 3;
         } else {
             CsrView<S> A{int32_t(n), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
             if constexpr (!Sc<S>::is_complex) {
-                if (spmm_tile) spmm_tile<<<grid, B, tile_smem, st>>>(A, ba, tile_cap);
-                else spmm<<<grid, B, 0, st>>>(A, ba);
+                if (spmm_tile) launch_pdl(m.pdl, st, spmm_tile, dim3(grid), dim3(B), tile_smem, A, ba, tile_cap);
+                else launch_pdl(m.pdl, st, spmm, dim3(grid), dim3(B), 0, A, ba);
             } else {
-                spmm<<<grid, B, 0, st>>>(A, ba);
+                launch_pdl(m.pdl, st, spmm, dim3(grid), dim3(B), 0, A, ba);
             }
             res.launches += 2;
         }
-        block_control_kernel<1024><<<1, 1024, 0, st>>>(ba.st, ba.partials, grid, K, Sc<S>::is_complex ? 1 : 0, 0);
+        launch_pdl(m.pdl, st, block_control_kernel<1024>, dim3(1), dim3(1024), 0, ba.st, ba.partials, grid, K,
+                   Sc<S>::is_complex ? 1 : 0, 0);
     };
 
     const int poll = std::max(1, env_int("EIGSOL_B200_BLOCK_POLL", 16));
