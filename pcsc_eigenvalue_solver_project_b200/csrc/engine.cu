@@ -59,6 +59,17 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? std::atoi(v) : dflt;
 }
 
+// Host threads feeding the pinned staging buffers of an upload.  One GPU: half the cores, 2..8 (C5 one-shot call on
+// a 16-core box: 2 threads 940 it/s, 4: 1100, 8: 1200); several ranks share the host, so each keeps 2.
+static int upload_threads(int nranks) {
+    int dflt = 2;
+    if (nranks == 1) {
+        const unsigned hw = std::thread::hardware_concurrency();
+        dflt = int(std::min(8u, std::max(2u, hw / 2)));
+    }
+    return std::max(1, env_int("EIGSOL_B200_UPLOAD_THREADS", dflt));
+}
+
 static void require_device() {
     int n = 0;
     const cudaError_t e = cudaGetDeviceCount(&n);
@@ -530,7 +541,7 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         up.add(d_outer.p, outer, sizeof(int32_t) * size_t(cols + 1));
         up.add(d_inner.p, inner, sizeof(int32_t) * size_t(nnz));
         up.add(d_cvals.p, values, size_t(nnz) * s);
-        EIGSOL_CUDA(up.run(device, env_int("EIGSOL_B200_UPLOAD_THREADS", 2)));
+        EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
         tr.mark("ingest: staged upload");
         const int B = 256;
         const unsigned gnz = unsigned((nnz + B - 1) / B);
@@ -613,7 +624,7 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     up.add(d_rowptr.p, rowptr, sizeof(int32_t) * size_t(nloc + 1));
     up.add(d_colidx.p, colidx, sizeof(int32_t) * size_t(nnz));
     up.add(d_vals.p, values, size_t(nnz) * s);
-    EIGSOL_CUDA(up.run(device, env_int("EIGSOL_B200_UPLOAD_THREADS", 2)));
+    EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
     tr.mark("rows(dev): staged upload");
     const int B = 256;
     const unsigned gnz = unsigned((std::max<int64_t>(nnz, 1) + B - 1) / B);
