@@ -272,13 +272,28 @@ inline FileMatrixHost read_matrix_text(const char* path, int dtype) {
     if (reason == 3) throw IoError("Failed to read scalar entry in sparse matrix");
 
     // CSC with rows ascending inside a column (what insert() + makeCompressed() leave, :120-131)
+    // counting sort by column, every phase split over the threads by COLUMN range: a thread scans all entries
+    // (sequential reads) and handles the ones whose column is its own, so file order is kept inside a column
+    // and no two threads touch the same counter
+    const int nt2 = io_threads(size_t(nnz) * 16);
     m.outer.assign(size_t(cols) + 1, 0);
-    for (int64_t k = 0; k < nnz; ++k) ++m.outer[size_t(ec[size_t(k)]) + 1];
+    parallel_for_threads(nt2, [&](int t) {
+        const int64_t j0 = cols * t / nt2, j1 = cols * (t + 1) / nt2;
+        for (int64_t k = 0; k < nnz; ++k) {
+            const int32_t c = ec[size_t(k)];
+            if (c >= j0 && c < j1) ++m.outer[size_t(c) + 1];
+        }
+    });
     for (int64_t j = 0; j < cols; ++j) m.outer[size_t(j) + 1] += m.outer[size_t(j)];
     std::vector<int32_t> cursor(m.outer.begin(), m.outer.end() - 1);
     std::vector<int32_t> order(nz);
-    for (int64_t k = 0; k < nnz; ++k) order[size_t(cursor[size_t(ec[size_t(k)])]++)] = int32_t(k);
-    const int nt2 = io_threads(size_t(nnz) * 16);
+    parallel_for_threads(nt2, [&](int t) {
+        const int64_t j0 = cols * t / nt2, j1 = cols * (t + 1) / nt2;
+        for (int64_t k = 0; k < nnz; ++k) {
+            const int32_t c = ec[size_t(k)];
+            if (c >= j0 && c < j1) order[size_t(cursor[size_t(c)]++)] = int32_t(k);
+        }
+    });
     std::atomic<int> dup{0};
     parallel_for_threads(nt2, [&](int t) {
         const int64_t j0 = cols * t / nt2, j1 = cols * (t + 1) / nt2;
@@ -293,11 +308,15 @@ inline FileMatrixHost read_matrix_text(const char* path, int dtype) {
     if (dup.load()) throw IoError("Duplicate (row, column) entry in sparse matrix");  // the reference's insert() forbids it
     m.inner.resize(size_t(nnz));
     m.values.resize(size_t(nnz) * size_t(per));
-    for (int64_t q = 0; q < nnz; ++q) {
-        const int32_t k = order[size_t(q)];
-        m.inner[size_t(q)] = er[size_t(k)];
-        for (int c2 = 0; c2 < per; ++c2) m.values[size_t(q) * size_t(per) + size_t(c2)] = ev[size_t(k) * size_t(per) + size_t(c2)];
-    }
+    parallel_for_threads(nt2, [&](int t) {
+        const int64_t q0 = nnz * t / nt2, q1 = nnz * (t + 1) / nt2;
+        for (int64_t q = q0; q < q1; ++q) {
+            const int32_t k = order[size_t(q)];
+            m.inner[size_t(q)] = er[size_t(k)];
+            for (int c2 = 0; c2 < per; ++c2)
+                m.values[size_t(q) * size_t(per) + size_t(c2)] = ev[size_t(k) * size_t(per) + size_t(c2)];
+        }
+    });
     return m;
 }
 
