@@ -334,6 +334,9 @@ EB_HDN bool eig_values_coop(const Cx* H, int k, Cx* theta, Cx* work, int lane, i
 // real and positive) of the general matrix H.  H is not modified.  false: the QR iteration failed.
 EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
     Cx M[kBlockElems], Z[kBlockElems], V[kBlockElems];
+    for (int i = 0; i < k; ++i)
+        for (int j = 0; j < k; ++j)  // fmax() in eig_scale skips NaN: look at every entry here
+            if (!(fabs(H[i * kBlockLd + j].re) < HUGE_VAL) || !(fabs(H[i * kBlockLd + j].im) < HUGE_VAL)) return false;
     // work on H * 2^-e with 2^e ~ max|h_ij| (exact; the Ritz values are multiplied back at the end), so the
     // plain sqrt / reciprocal forms above can neither overflow nor underflow
     double hs, hback;
@@ -355,7 +358,7 @@ EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
             for (int p = r + 1; p <= i; ++p) s = s + M[r * kBlockLd + p] * V[p * kBlockLd + i];
             Cx den = M[r * kBlockLd + r] - lam;
             if (cabs1(den) < small) den = cx(small);
-            V[r * kBlockLd + i] = -cdiv_fast(s, den);
+            V[r * kBlockLd + i] = -(s / den);  // Smith's division: den may be as small as 1e-300 (H = 0)
         }
     }
     int ord[kBlockMax];

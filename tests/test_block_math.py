@@ -169,3 +169,61 @@ def test_block_iteration_max_trips_zero_and_breakdown():
     assert stop == 2 and not conv  # A Q = 0: the block counterpart of normY == 0
     same = np.ones((4, 2))
     assert bs.block_power_cpu(lambda q: a @ q, same, 2, 5, 1e-10)[4] == 2  # rank-deficient start block
+
+
+# ---- edge cases of the k x k eigen-solver (it runs unattended on the device between two launches) -------------
+def test_eig_edge_cases_zero_identity_jordan_nan():
+    ok, th, s = bs.eig(np.zeros((4, 4)))
+    assert ok and np.all(th == 0) and np.allclose(np.abs(s).max(axis=0), 1.0)
+    ok, th, s = bs.eig(np.eye(5) * (2 - 3j))
+    assert ok and np.allclose(th, 2 - 3j) and np.allclose(s.conj().T @ s, np.eye(5), atol=1e-14)
+    j = np.diag(np.full(6, 1.5)) + np.diag(np.ones(5), 1)          # one Jordan block: defective
+    ok, th, s = bs.eig(j)
+    assert ok and np.allclose(th, 1.5, atol=1e-2)                  # eigenvalues of a 6 x 6 Jordan block move by eps^(1/6)
+    for bad in (np.nan, np.inf):
+        h = np.eye(3)
+        h[1, 2] = bad
+        assert not bs.eig(h)[0]
+
+
+@pytest.mark.parametrize("scale", [1e300, 1e-300, 2.0 ** 1000, 2.0 ** -1000])
+def test_eig_is_scale_invariant(scale):
+    rng = np.random.default_rng(8)
+    h = rnd(rng, 6)
+    ok0, th0, s0 = bs.eig(h)
+    ok1, th1, s1 = bs.eig(h * scale)
+    assert ok0 and ok1
+    if scale in (2.0 ** 1000, 2.0 ** -1000):   # a power of two inside the clamp: bit-identical values
+        assert np.array_equal(th1 / scale, th0) and np.array_equal(s1, s0)
+    else:
+        assert np.allclose(th1 / scale, th0, rtol=1e-12) and np.allclose(s1, s0, atol=1e-9)
+
+
+@pytest.mark.parametrize("k", [2, 4, 8])
+def test_eig_clustered_and_graded_spectra(k):
+    rng = np.random.default_rng(40 + k)
+    for _ in range(30):
+        q, _ = np.linalg.qr(rnd(rng, k))
+        d = np.concatenate([[1.0, 1.0 + 1e-13], 10.0 ** -rng.integers(0, 12, k - 2)])[:k] * np.exp(1j * rng.uniform(0, 6.28, k))
+        h = q @ np.diag(d) @ q.conj().T                           # normal matrix: eigenvalues are well conditioned
+        ok, th, s = bs.eig(h)
+        assert ok
+        ref = sorted(d, key=abs, reverse=True)
+        assert np.allclose(np.sort(np.abs(th))[::-1], np.abs(ref), rtol=1e-9, atol=1e-13)
+        for j in range(k):
+            assert np.linalg.norm(h @ s[:, j] - th[j] * s[:, j]) < 1e-12
+
+
+def test_values_only_path_matches_full_decomposition():
+    """The loop uses eig_values_coop (no vectors, window-confined rotations); the result step uses eig_general.
+    block_power_cpu exercises the former, bs.eig the latter: the Ritz values must agree bit for bit."""
+    rng = np.random.default_rng(77)
+    a = rng.standard_normal((40, 40)) + 1j * rng.standard_normal((40, 40))
+    x0 = rng.standard_normal((40, 4)) + 1j * rng.standard_normal((40, 4))
+    th, x, it, conv, stop = bs.block_power_cpu(lambda q: a @ q, x0, 4, 25, -1.0)
+    q, _ = np.linalg.qr(x)                                          # the Ritz vectors span the final Q
+    # recompute H of the final launch from the returned vectors' span and compare spectra (order-insensitive, loose):
+    h = q.conj().T @ a @ q
+    assert np.allclose(np.sort_complex(np.linalg.eigvals(h)), np.sort_complex(th), rtol=1e-8)
+    for j in range(4):
+        assert abs(np.linalg.norm(x[:, j]) - 1) < 1e-12
