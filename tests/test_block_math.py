@@ -227,3 +227,23 @@ def test_values_only_path_matches_full_decomposition():
     assert np.allclose(np.sort_complex(np.linalg.eigvals(h)), np.sort_complex(th), rtol=1e-8)
     for j in range(4):
         assert abs(np.linalg.norm(x[:, j]) - 1) < 1e-12
+
+
+# ---- host-side behaviour of the Python entry point (no GPU needed) ---------------------------------------------
+def test_block_power_method_checks_come_before_any_device_work():
+    import pcsc_eigenvalue_solver_project_b200 as es
+    with pytest.raises(RuntimeError, match="powerMethod: matrix must be square"):      # power_method.hpp:52-55
+        es.blockPowerMethod(es.Matrix(np.zeros((2, 3))), 2)
+    with pytest.raises(RuntimeError, match="powerMethod: matrix has zero size"):       # power_method.hpp:56-58
+        es.blockPowerMethod(es.Matrix(np.zeros((0, 0))), 2)
+
+
+def test_random_block_columns_are_the_reference_start_vectors():
+    import pcsc_eigenvalue_solver_project_b200 as es
+    xb = es.random_block(50, 4, np.float64, seed=3)
+    assert xb.shape == (50, 4) and xb.flags.f_contiguous
+    for j in range(4):
+        assert np.array_equal(xb[:, j], es.random_unit(50, np.float64, seed=3 + j))   # power_method.hpp:62 after srand(seed + j)
+        assert abs(np.linalg.norm(xb[:, j]) - 1) < 1e-14
+    zb = es.random_block(20, 2, np.complex128, seed=1)
+    assert zb.dtype == np.complex128 and np.linalg.matrix_rank(zb) == 2
