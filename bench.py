@@ -60,6 +60,44 @@ def workload_order(name):
     return {"c2": int(g or 1024) ** 2, "c3": int(g or 8192), "c4": int(g or 2048) ** 2, "c5": int(g or 256) ** 3}[name]
 
 
+def workload_nnz(name, n):
+    g = int(os.environ.get("BENCH_GRID", 0))
+    if name == "c2":
+        g = g or 1024
+        return 5 * n - 4 * g
+    if name == "c4":
+        g = g or 2048
+        return 5 * n - 4 * g
+    if name == "c5":
+        g = g or 256
+        return 7 * n - 6 * g * g
+    return n * n
+
+
+def workload_config(name):
+    """`config` of the JSON line: identical in both arms (the launch geometry of the GPU arm is under `launch`)."""
+    n = workload_order(name)
+    return {"workload": WORKLOADS[name], "n": n, "nnz": workload_nnz(name, n),
+            "l2": "inputs larger than L2 (1.74 GB per matvec)" if name == "c5" else
+                  ("matrix + vectors larger than L2" if name in ("c3", "c4") else "working set ~ L2 size: effective GB/s"),
+            "x0": "Eigen Random after srand(1)", "tolerance": -1.0}
+
+
+def golden_lambda(name, trips):
+    """Eigenvalue of the compiled reference after `trips` fixed trips (tests/golden/bench_lambda.json), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "tests", "golden", "bench_lambda.json")))["lambda"].get(f"{name}_{trips}")
+        return complex(t[0], t[1]) if t else None
+    except Exception:
+        return None
+
+
+def parity_of(lam, ref, trips, source):
+    lam, ref = complex(lam), complex(ref)
+    return {"lambda_rel_err": abs(lam - ref) / abs(ref), "trips": trips, "lambda": repr(lam), "reference_lambda": repr(ref),
+            "reference": source, "tolerance": 1e-10, "ok": bool(abs(lam - ref) <= 1e-10 * abs(ref))}
+
+
 def alg_bytes_global(name, n, nnz):
     ss = 16 if DTYPES[name] == "c128" else 8
     if name == "c3":
@@ -132,10 +170,10 @@ def recorded_traffic(name, nranks):
 # reference arm / cpu_baseline: the reference's own powerMethod on host cores (single-threaded by
 # construction: eigen/Eigen/src/SparseCore/SparseDenseProduct.h:94-111 has no OpenMP branch).
 # --------------------------------------------------------------------------------------------------
-def reference_rate(name, budget_s, max_trips):
+def reference_rate(name, budget_s, max_trips, warmup=1):
     """iterations/s of EigSol::powerMethod (oracle/_ref) on the full workload matrix, same x0 seed,
     tolerance = -1 (fixed trips).  The sample is `trips` reference iterations of the FULL matrix;
-    x0 generation is subtracted with a 0-trip call."""
+    x0 generation is subtracted with a 0-trip call.  `warmup` untimed trips run first."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from _oracle import REF_SO, Reference
     from pcsc_eigenvalue_solver_project_b200 import generators as gen
@@ -158,6 +196,8 @@ def reference_rate(name, budget_s, max_trips):
     t1 = ref.power(h, dt, n, 1, 1, -1.0, want_x=False)[5]
     per_trip = max(t1 - t0, 1e-9)
     trips = int(max(1, min(max_trips, budget_s / per_trip)))
+    if warmup > 1:  # the 1-trip probe above already is one warm-up trip
+        ref.power(h, dt, n, 1, int(min(warmup - 1, max(1, budget_s / 4 / per_trip))), -1.0, want_x=False)
     st, lam, _, iters, _, sec = ref.power(h, dt, n, 1, trips, -1.0, want_x=False)
     ref.destroy(h)
     assert st == 0 and iters == trips
@@ -174,20 +214,20 @@ def reference_rate(name, budget_s, max_trips):
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
-    cfg = {"workload": WORKLOADS[args.workload], "inputs": "larger than L2" if args.workload != "c2" else "L2-sized"}
+    cfg = workload_config(args.workload)
     try:
-        cb = reference_rate(args.workload, budget_s=float(os.environ.get("BENCH_REF_BUDGET_S", 45)),
-                            max_trips=max(1, args.steps))
+        cb = reference_rate(args.workload, budget_s=float(os.environ.get("BENCH_REF_BUDGET_S", 60)),
+                            max_trips=max(1, args.steps), warmup=args.warmup)
     except Exception as e:  # the oracle always exists; this is a packaging error worth seeing
         emit({"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"})
         return
     line = {"impl": "reference", "metric": "power_iterations_per_s", "value": cb["value"], "unit": "iter/s",
-            "n_gpus": args.gpus, "steps": cb["trips"], "warmup": 1, "ms_per_step": 1e3 / cb["value"],
+            "n_gpus": args.gpus, "steps": cb["trips"], "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": DTYPES[args.workload],
             "data": "synthetic", "config": cfg,
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "lambda": cb["lambda"]}
     emit(line)
 
 
@@ -245,11 +285,13 @@ def main():
 
     comm = None
     dist = None
+    cpu_group = None
     if world > 1:
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+        cpu_group = dist.new_group(backend="gloo")  # host-side barrier: waiting ranks leave their GPUs idle
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idt.copy_(torch.frombuffer(bytearray(es.Comm.unique_id()), dtype=torch.uint8))
@@ -259,6 +301,10 @@ def main():
     def barrier():
         if dist is not None:
             dist.barrier()
+
+    def cpu_barrier():
+        if dist is not None:
+            dist.barrier(group=cpu_group)
 
     name = args.workload
     n = workload_order(name)
@@ -315,40 +361,41 @@ def main():
                 "note": "per-rank bytes / step time" if world > 1 else "one launch per step"}
 
     # ---- e2e: the reference-facing call with host buffers ----
+    # powerMethod(Matrix, SolverOptions) in ONE process, exactly what a caller of the reference writes.  On N > 1 GPUs
+    # rank 0 makes that call with EIGSOL_B200_NGPU=N (the library shards the solve over the N devices itself,
+    # single-process group); the other ranks wait on a host-side barrier with idle GPUs.
     e2e = None
     if not args.no_e2e:
         opts = es.SolverOptions(args.steps, -1.0)
         M = None
-        if world == 1 and name == "c3":
-            M = es.Matrix(host["a"])  # the reference's Matrix also stores by value (matrix.hpp:187-195)
-            h2d = host["a"].nbytes + x0.nbytes
-        elif world == 1:
-            outer, inner, vals = gen.csr_to_csc_hermitian(host["rp"], host["ci"], host["v"])
-            M = es.Matrix(((n, n), outer, inner, vals))
-            h2d = outer.nbytes + inner.nbytes + vals.nbytes + x0.nbytes
-        barrier()
-        t0 = time.perf_counter()
-        if M is not None:
-            r = es.powerMethod(M, opts, x0=x0)
-        else:
+        if rank == 0:
             if name == "c3":
-                d2 = es.DeviceMatrix.from_matrix(es.Matrix(host["a"]), comm)
-                h2d = host["a"].nbytes // world + x0.nbytes
+                M = es.Matrix(host["a"])  # the reference's Matrix also stores by value (matrix.hpp:187-195)
+                h2d = host["a"].nbytes + x0.nbytes
             else:
-                d2 = es.DeviceMatrix.from_csr_rows(n, host["lo"], host["rp"], host["ci"], host["v"], comm)
-                h2d = host["rp"].nbytes + host["ci"].nbytes + host["v"].nbytes + x0.nbytes
-            r = d2.power(x0, opts)
-            d2.close()
-        barrier()
-        t_e2e = time.perf_counter() - t0
-        if comm is not None:
-            t_e2e = comm.max_float(t_e2e)
-        assert r.iterations == args.steps
-        e2e = {"value": args.steps / t_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d * world / args.steps,
-               "d2h_bytes_per_step": x0.nbytes * world / args.steps, "seconds": t_e2e, "lambda": repr(r.eigenvalue),
-               "call": "powerMethod(Matrix, SolverOptions{steps, -1}) one-shot: matrix + x0 uploaded, "
-                       "CSC->CSR, steps trips, eigenvector downloaded" if world == 1 else
-                       "DeviceMatrix.from_csr_rows + power per rank: rows + x0 uploaded, steps trips, eigenvector gathered"}
+                if world > 1:
+                    _, rp, ci, v = workload_rows(name, gen)
+                else:
+                    rp, ci, v = host["rp"], host["ci"], host["v"]
+                outer, inner, vals = gen.csr_to_csc_hermitian(rp, ci, v)
+                M = es.Matrix(((n, n), outer, inner, vals))
+                h2d = outer.nbytes + inner.nbytes + vals.nbytes + x0.nbytes
+                del rp, ci, v
+        cpu_barrier()
+        if rank == 0:
+            os.environ["EIGSOL_B200_NGPU"] = str(world)
+            t0 = time.perf_counter()
+            r = es.powerMethod(M, opts, x0=x0)
+            t_e2e = time.perf_counter() - t0
+            os.environ["EIGSOL_B200_NGPU"] = "1"
+            assert r.iterations == args.steps
+            e2e = {"value": args.steps / t_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d / args.steps,
+                   "d2h_bytes_per_step": x0.nbytes / args.steps, "seconds": t_e2e, "lambda": repr(r.eigenvalue),
+                   "call": "powerMethod(Matrix, SolverOptions{steps, -1}) one-shot in one process: matrix + x0 uploaded, "
+                           "CSC->CSR, steps trips, eigenvector downloaded" +
+                           (f"; EIGSOL_B200_NGPU={world}: the library shards the call over {world} GPUs" if world > 1 else "")}
+            del M
+        cpu_barrier()
 
     if rank != 0:
         dm.close()
@@ -357,24 +404,40 @@ def main():
         return
 
     cpu_baseline = None
+    parity = None
     if world == 1 and not args.no_cpu_baseline:
         del host
         try:
             cb = reference_rate(name, budget_s=float(os.environ.get("BENCH_CPU_BUDGET_S", 20)), max_trips=20)
             cpu_baseline = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            # parity (outside every timed region): the GPU path on the resident matrix for exactly the trips the
+            # reference just ran, same x0 -- eigenvalue within the north star's 1e-10
+            rp_ = dm.power(x0, es.SolverOptions(cb["trips"], -1.0))
+            parity = parity_of(rp_.eigenvalue, complex(cb["lambda"]), cb["trips"],
+                               "EigSol::powerMethod (oracle/_ref) run beside the bench")
         except Exception as e:
             cpu_baseline = {"value": None, "unit": "iter/s", "cores": 1, "kind": "reference",
                             "sample": f"unavailable: {type(e).__name__}: {e}"}
+    if parity is None and e2e is not None:
+        gl = golden_lambda(name, args.steps)
+        if gl is not None:
+            parity = parity_of(complex(e2e["lambda"]), gl, args.steps,
+                               "tests/golden/bench_lambda.json (compiled reference, generated in the authoring container)")
+    # a read-dominated HBM ceiling measured in the same run (12 read planes per written plane = the matvec's mix)
+    try:
+        roofline["peak_read_mix"] = es.hbm_probe(128 << 20, 12, 20)[0]
+        roofline["frac_of_read_mix"] = achieved / roofline["peak_read_mix"]
+    except Exception as e:  # measurement extra: never fails the bench
+        roofline["peak_read_mix"] = None
+        sys.stderr.write(f"hbm_probe: {e}\n")
 
     line = {"metric": "power_iterations_per_s", "value": value, "unit": "iter/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": DTYPES[name], "data": "synthetic",
-            "config": {"workload": WORKLOADS[name], "n": n, "nnz": nnz, "partition": f"rows/{world}",
-                       "l2": "inputs larger than L2 (1.74 GB per matvec)" if name == "c5" else
-                             ("matrix + vectors larger than L2" if name in ("c3", "c4") else "working set ~ L2 size: effective GB/s"),
-                       "x0": "Eigen Random after srand(1)", "tolerance": -1.0, "kernel": info["kernel_name"],
-                       "grid": info["grid"], "block": info["block"], "halo_per_rank": info["halo"]},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches,
+            "config": workload_config(name),
+            "launch": {"partition": f"rows/{world}", "kernel": info["kernel_name"], "grid": info["grid"],
+                       "block": info["block"], "halo_per_rank": info["halo"], "exchange": info["exchange"]},
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "parity": parity, "gpu_launches": launches,
             "clocks": clocks, "lambda": repr(res.eigenvalue), "trips_done": res.iterations, "build_s": round(t_build, 2)}
     emit(line)
     dm.close()

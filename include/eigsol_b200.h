@@ -135,8 +135,15 @@ EIGSOL_B200_API int eigsol_b200_power_dense(int dtype, int64_t rows, int64_t col
 
 /* ---- handle API: upload once, iterate many (device-resident Matrix; bench + repeated callers) -- */
 
-/* comm may be NULL (single GPU, current/first device).  With a comm, EVERY rank passes the same
- * global matrix; the library keeps this rank's nnz-balanced row block. */
+/* comm == NULL: the calling process owns the whole solve.  By default that is ONE GPU (the calling thread's
+ * current device).  With the environment variable EIGSOL_B200_NGPU=P (P <= 8, <= visible devices) the handle
+ * becomes a SINGLE-PROCESS GROUP: the library row-shards the matrix over P devices (starting at the current one),
+ * drives each from its own host thread, and runs the same fused matvec + halo-exchange + all-reduce kernel over
+ * peer memory as a process-per-GPU group does -- the caller, e.g. the unmodified EigSol::powerMethod(M, opts), sees
+ * one handle and global vectors.  Matrices with fewer than EIGSOL_B200_MIN_ROWS_PER_GPU (1024) rows per device use
+ * fewer devices.  One-shot calls (eigsol_b200_power_csc / _dense) follow the same rule.
+ * With a comm (one process per GPU), EVERY rank passes the same global matrix; the library keeps this rank's
+ * nnz-balanced row block. */
 EIGSOL_B200_API int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols,
                                                   const int32_t* outer, const int32_t* inner,
                                                   const void* values, eigsol_b200_comm* comm,
@@ -173,8 +180,9 @@ EIGSOL_B200_API int eigsol_b200_power_run(eigsol_b200_matrix* m, const void* x0,
 /* Stepwise form of the same loop (device-resident between calls):
  *   begin : upload x0, reset the iteration state (max_iterations / tolerance as in power_run)
  *   step  : issue up to `trips` further power iterations; *ms_out (may be NULL) = device time of
- *           those launches measured with CUDA events on the launching stream; *kernel_ms_out (may be
- *           NULL) = device time of the matvec kernel alone, averaged per launch (single GPU only)
+ *           those launches measured with CUDA events on the launching stream (a multi-GPU rank first passes
+ *           a device-side barrier of the ranks, so the timers of all ranks start together; a single-process
+ *           group returns the slowest rank's time)
  *   end   : normalise and download the current eigenvector and the state                         */
 EIGSOL_B200_API int eigsol_b200_power_begin(eigsol_b200_matrix* m, const void* x0, int max_iterations,
                                             double tolerance);
@@ -216,7 +224,27 @@ EIGSOL_B200_API int eigsol_b200_block_power_run(eigsol_b200_matrix* m, int block
 /* Total kernel launches this handle has issued (bench.py's gpu_launches claim). */
 EIGSOL_B200_API int64_t eigsol_b200_matrix_launch_count(const eigsol_b200_matrix* m);
 
-/* ---- multi-GPU: one rank per GPU (one process per GPU under torchrun, or one thread per GPU) ---- */
+/* Matrix handles created by this process so far (every one is an upload of a whole matrix): lets a caller -- and the
+ * tests of the drop-in Matrix cache -- see that repeated solves on one EigSol::Matrix upload once. */
+EIGSOL_B200_API int64_t eigsol_b200_matrices_created(void);
+
+/* Multi-GPU diagnostics (library built-in, enabled by EIGSOL_B200_PEER_STATS=1 at matrix creation; zeros otherwise):
+ * where this rank's trips waited since the previous call, in nanoseconds of the GPU's global timer.
+ *   out[0] control CTA: time between publishing its flag and holding every peer's flag, summed over launches
+ *   out[1] launches counted in out[0]
+ *   out[2] matvec warps that reached a halo unit before the owner's flag: time spun, summed     out[3] such warps
+ *   out[4] longest single halo wait            out[5] matvec warps that reached a halo unit (waited or not) */
+EIGSOL_B200_API int eigsol_b200_matrix_peer_stats(eigsol_b200_matrix* m, uint64_t out[8]);
+
+/* Measurement only (nothing on the path calls it): HBM throughput of a read-dominated stream -- `planes`
+ * (1, 4, 8 or 12) coalesced read planes of plane_bytes summed into one written plane, 128-bit loads -- in GB/s
+ * counted over read + written bytes; best and mean of `reps` launches timed with CUDA events.  12 planes is the
+ * 92 / 8 read/write mix of an fp64 CSR matvec; bench.py prints it as roofline.peak_read_mix. */
+EIGSOL_B200_API int eigsol_b200_hbm_probe(int64_t plane_bytes, int planes, int reps, double* best_gbps,
+                                          double* mean_gbps);
+
+/* ---- multi-GPU, one PROCESS per GPU (torchrun / MPI): every process creates a comm and passes it to the
+ * ---- matrix constructors.  (One process driving several GPUs needs no comm: see EIGSOL_B200_NGPU above.) ---- */
 
 /* 128-byte NCCL unique id; rank 0 creates it, the host program broadcasts it. */
 EIGSOL_B200_API int eigsol_b200_comm_unique_id(void* id128);

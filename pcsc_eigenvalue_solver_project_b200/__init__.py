@@ -28,7 +28,7 @@ from ._capi import (C128, F64, KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_STREAM
 
 __all__ = ["Matrix", "SolverOptions", "EigenResult", "powerMethod", "power_method", "DeviceMatrix", "Comm",
            "BlockEigenResult", "blockPowerMethod", "random_block",
-           "random_unit", "srand", "device_count", "EigsolB200Error", "readMatrixFromFile",
+           "random_unit", "srand", "device_count", "hbm_probe", "EigsolB200Error", "readMatrixFromFile",
            "writeMatrixBinary", "readMatrixBinary"]
 
 
@@ -63,6 +63,14 @@ class BlockEigenResult:
 
 def device_count() -> int:
     return int(_capi.lib().eigsol_b200_device_count())
+
+
+def hbm_probe(plane_bytes: int = 128 << 20, planes: int = 12, reps: int = 20) -> tuple[float, float]:
+    """(best, mean) GB/s of a read-dominated stream: ``planes`` read planes summed into one written plane
+    (12 = the 92/8 read/write mix of an fp64 CSR matvec).  Measurement only; bench.py's ``peak_read_mix``."""
+    best, mean = C.c_double(0.0), C.c_double(0.0)
+    _capi.check(_capi.lib().eigsol_b200_hbm_probe(int(plane_bytes), int(planes), int(reps), C.byref(best), C.byref(mean)))
+    return float(best.value), float(mean.value)
 
 
 _libc = C.CDLL(None)
@@ -364,6 +372,13 @@ class DeviceMatrix:
 
     def launch_count(self) -> int:
         return int(_capi.lib().eigsol_b200_matrix_launch_count(self._h))
+
+    def peer_stats(self) -> dict:
+        """Where this rank's multi-GPU trips waited since the last call (needs EIGSOL_B200_PEER_STATS=1 at creation)."""
+        out = np.zeros(8, dtype=np.uint64)
+        _capi.check(_capi.lib().eigsol_b200_matrix_peer_stats(self._h, _capi.ptr(out)))
+        return {"control_wait_ns": int(out[0]), "control_launches": int(out[1]), "halo_wait_ns": int(out[2]),
+                "halo_waiting_warps": int(out[3]), "halo_wait_max_ns": int(out[4]), "halo_warps": int(out[5])}
 
     @property
     def dtype(self):

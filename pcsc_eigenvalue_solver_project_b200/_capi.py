@@ -27,6 +27,7 @@ EXPORTS = [
     "eigsol_b200_matrix_destroy", "eigsol_b200_matrix_get_info", "eigsol_b200_matrix_set_kernel",
     "eigsol_b200_power_run", "eigsol_b200_power_begin", "eigsol_b200_power_step", "eigsol_b200_power_end",
     "eigsol_b200_matvec", "eigsol_b200_rayleigh", "eigsol_b200_block_power_run", "eigsol_b200_matrix_launch_count",
+    "eigsol_b200_matrix_peer_stats", "eigsol_b200_hbm_probe", "eigsol_b200_matrices_created",
     "eigsol_b200_read_matrix_text", "eigsol_b200_read_matrix_bin", "eigsol_b200_write_matrix_bin",
     "eigsol_b200_file_matrix_release",
     "eigsol_b200_comm_unique_id", "eigsol_b200_comm_create", "eigsol_b200_comm_destroy",
@@ -103,6 +104,9 @@ def lib():
         "eigsol_b200_rayleigh": (i, [vp, vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "eigsol_b200_block_power_run": (i, [vp, i, i, vp, i, C.c_double, vp, dp, ip, ip, ip, fp]),
         "eigsol_b200_matrix_launch_count": (i64, [vp]),
+        "eigsol_b200_matrix_peer_stats": (i, [vp, vp]),
+        "eigsol_b200_matrices_created": (i64, []),
+        "eigsol_b200_hbm_probe": (i, [i64, i, i, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "eigsol_b200_read_matrix_text": (i, [C.c_char_p, i, C.POINTER(FileMatrix)]),
         "eigsol_b200_read_matrix_bin": (i, [C.c_char_p, C.POINTER(FileMatrix)]),
         "eigsol_b200_write_matrix_bin": (i, [C.c_char_p, i, i, i64, i64, i64, vp, vp, vp]),

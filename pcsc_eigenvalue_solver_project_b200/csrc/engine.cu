@@ -5,7 +5,10 @@
 // issues launches and polls the device-resident PowerState; no arithmetic of the path runs on the CPU
 // and there is no CPU fallback: without a CUDA device every compute entry point fails loudly.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <functional>
 #include <cstdio>
 #include <climits>
 #include <cstdlib>
@@ -13,6 +16,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/eigsol_b200.h"
@@ -20,18 +24,69 @@
 #include "ingest.cuh"
 #include "kernels.cuh"
 #include "plan.hpp"
+#include "probe.cuh"
 #include "runtime.hpp"
 
 namespace eigsol_b200 {
 
 static thread_local std::string g_last_error;
+static std::atomic<int64_t> g_matrices_created{0};  // device uploads of whole matrices so far (tests of the Matrix cache)
 
 // -------------------------------------------------------------------------------------------------
-// One rank of a multi-GPU group.
+// Meeting point of the P ranks of a SINGLE-PROCESS group (one host thread per GPU, EIGSOL_B200_NGPU=P): the
+// setup-time collectives of a process-per-GPU group (NCCL below) become exchanges through this object.
+// -------------------------------------------------------------------------------------------------
+struct LocalGroup {
+    explicit LocalGroup(int n) : nranks(n), slot(size_t(n), nullptr) {}
+    const int nranks;
+    std::mutex mu;
+    std::condition_variable cv;
+    int arrived = 0;
+    uint64_t generation = 0;
+    bool failed = false;             // a rank left with an exception: every barrier now throws instead of waiting
+    std::vector<const void*> slot;   // slot[r]: what rank r shows its peers in the current exchange
+
+    void barrier() {
+        std::unique_lock<std::mutex> lk(mu);
+        if (failed) throw DeviceError("powerMethod: device error: another GPU of the group failed");
+        const uint64_t gen = generation;
+        if (++arrived == nranks) {
+            arrived = 0;
+            ++generation;
+            cv.notify_all();
+            return;
+        }
+        cv.wait(lk, [&] { return generation != gen || failed; });
+        if (generation == gen) throw DeviceError("powerMethod: device error: another GPU of the group failed");
+    }
+    void fail() {
+        std::lock_guard<std::mutex> lk(mu);
+        failed = true;
+        cv.notify_all();
+    }
+    void reset() {
+        std::lock_guard<std::mutex> lk(mu);
+        failed = false;
+        arrived = 0;
+    }
+    // every rank shows `mine`, runs `body(slots)` while all are visible, and leaves together
+    template <class F> void exchange(int rank, const void* mine, F&& body) {
+        slot[size_t(rank)] = mine;
+        barrier();
+        body(slot);
+        barrier();
+    }
+};
+
+// -------------------------------------------------------------------------------------------------
+// One rank of a multi-GPU group: a process-per-GPU rank (NCCL communicator, peers reached through CUDA IPC)
+// or one thread of a single-process group (`local`, peers reached through plain peer access).
 // -------------------------------------------------------------------------------------------------
 struct Comm {
     int rank = 0, nranks = 1, device = 0;
     ncclComm_t nccl_comm = nullptr;
+    LocalGroup* local = nullptr;
+    std::vector<int> local_devices;  // single-process group: CUDA device of every rank
     cudaStream_t stream = nullptr;
     DevBuf scratch;  // small device scratch for setup-time collectives
     ~Comm() {
@@ -59,15 +114,12 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? std::atoi(v) : dflt;
 }
 
-// Host threads feeding the pinned staging buffers of an upload.  One GPU: half the cores, 2..8 (C5 one-shot call on
-// a 16-core box: 2 threads 940 it/s, 4: 1100, 8: 1200); several ranks share the host, so each keeps 2.
+// Host threads feeding the pinned staging buffers of an upload: half the cores, shared by the ranks that run on this
+// host (one GPU on a 16-core box: 2 threads 940 it/s on the one-shot C5 call, 4: 1100, 8: 1200), 1..8 per rank.
 static int upload_threads(int nranks) {
-    int dflt = 2;
-    if (nranks == 1) {
-        const unsigned hw = std::thread::hardware_concurrency();
-        dflt = int(std::min(8u, std::max(2u, hw / 2)));
-    }
-    return std::max(1, env_int("EIGSOL_B200_UPLOAD_THREADS", dflt));
+    const unsigned hw = std::max(2u, std::thread::hardware_concurrency());
+    const int dflt = int(std::min(8u, std::max(1u, hw / 2 / unsigned(std::max(nranks, 1)))));
+    return std::max(1, env_int("EIGSOL_B200_UPLOAD_THREADS", std::max(dflt, nranks == 1 ? 2 : 1)));
 }
 
 static void require_device() {
@@ -88,6 +140,12 @@ static std::vector<int64_t> comm_allgather_i64(Comm* c, int64_t v) {
         out[0] = v;
         return out;
     }
+    if (c->local) {
+        c->local->exchange(c->rank, &v, [&](const std::vector<const void*>& sl) {
+            for (int r = 0; r < c->nranks; ++r) out[size_t(r)] = *static_cast<const int64_t*>(sl[size_t(r)]);
+        });
+        return out;
+    }
     int64_t* d = c->scratch.as<int64_t>();
     EIGSOL_CUDA(cudaMemcpyAsync(d + c->nranks + c->rank, &v, sizeof v, cudaMemcpyHostToDevice, c->stream));
     // AllGather may be absent from a very old libnccl; grouped broadcasts are equivalent
@@ -103,6 +161,12 @@ static std::vector<int64_t> comm_allgather_i64(Comm* c, int64_t v) {
 // all-gather of a fixed-size blob per rank (setup only): out[r * bytes ...] = rank r's blob
 static std::vector<char> comm_allgather_bytes(Comm* c, const void* mine, size_t bytes) {
     std::vector<char> out(bytes * size_t(c->nranks));
+    if (c->local) {
+        c->local->exchange(c->rank, mine, [&](const std::vector<const void*>& sl) {
+            for (int r = 0; r < c->nranks; ++r) std::memcpy(out.data() + bytes * size_t(r), sl[size_t(r)], bytes);
+        });
+        return out;
+    }
     DevBuf d;
     d.alloc(out.size());
     EIGSOL_CUDA(cudaMemcpyAsync(d.as<char>() + bytes * c->rank, mine, bytes, cudaMemcpyHostToDevice, c->stream));
@@ -119,6 +183,13 @@ static std::vector<char> comm_allgather_bytes(Comm* c, const void* mine, size_t 
 // min over ranks of an int (setup only): lets every rank take the same decision
 static int comm_min_int(Comm* c, int v) {
     if (c->nranks == 1) return v;
+    if (c->local) {
+        int mn = v;
+        c->local->exchange(c->rank, &v, [&](const std::vector<const void*>& sl) {
+            for (int r = 0; r < c->nranks; ++r) mn = std::min(mn, *static_cast<const int*>(sl[size_t(r)]));
+        });
+        return mn;
+    }
     int* d = reinterpret_cast<int*>(c->scratch.as<int64_t>() + 3 * c->nranks + 8);
     EIGSOL_CUDA(cudaMemcpyAsync(d, &v, sizeof v, cudaMemcpyHostToDevice, c->stream));
     EIGSOL_NCCL(nccl().AllReduce(d, d, 1, ncclInt32, ncclMin, c->nccl_comm, c->stream));
@@ -148,7 +219,8 @@ struct MatrixImpl {
     // x exchange + scalar all-reduce: MODE_FUSED (one GPU), MODE_SPLIT (NCCL), MODE_PEER (peer memory)
     int xmode = MODE_FUSED;
     PeerArgs peer_h{};
-    DevBuf d_peer, d_scal_in, d_flag_in;
+    DevBuf d_peer, d_scal_in, d_flag_in, d_stats;
+    unsigned long long gate_epoch = 0;  // MODE_PEER: gates passed so far (identical on every rank)
     std::vector<void*> ipc_opened;
 
     // sparse layouts
@@ -189,13 +261,14 @@ struct MatrixImpl {
     unsigned long long flag_epoch = 0;  // MODE_PEER: flag base of the current solve (identical on every rank)
     bool begun = false;
     int max_trips = 0;
-    cudaGraphExec_t graph = nullptr;
+    cudaGraphExec_t graph = nullptr, graph_short = nullptr;  // graph_len launches / kRing launches
     int graph_len = 0;
 
     int ss() const { return dtype ? 16 : 8; }
     ~MatrixImpl() {
         for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
         if (graph) cudaGraphExecDestroy(graph);
+        if (graph_short) cudaGraphExecDestroy(graph_short);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -207,6 +280,8 @@ struct MatrixImpl {
     void ensure_host_csr();
     void compute_prescale();
     void init_sparse_device_rows(const int32_t* rowptr, const int32_t* colidx, const void* values);
+    void finish_rows_on_device();
+    void init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner, const void* values);
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
     void plan_exchange();
     void setup_peer();
@@ -222,6 +297,7 @@ struct MatrixImpl {
         a.deferred = (xmode == MODE_PEER && have_deferred) ? d_deferred.as<uint8_t>() : nullptr;
         a.serpentine = serpentine;
         a.unit_start = (xmode == MODE_PEER && have_deferred) ? unit_start : 0;
+        a.halo_base = xmode == MODE_PEER ? int(nloc_pad) : INT32_MAX;
         return a;
     }
     void alloc_vectors();
@@ -234,6 +310,8 @@ struct MatrixImpl {
     void launch_matvec(int phase);
     void build_deferred();
     void issue_trips(int k);
+    void ensure_graphs();
+    void rank_barrier();
     void step(int trips, float* ms_out);
     void end(void* x_out, double lambda_out[2], int* iters, int* conv);
     const PowerState& poll_state();
@@ -289,42 +367,61 @@ void MatrixImpl::plan_exchange() {
     need_pack = false;
     if (nranks == 1) return;
     Comm* c = comm;
-    int64_t* d = c->scratch.as<int64_t>();
-    // counts: d[0..P) = what I need from each peer, d[P..2P) = what each peer needs from me
-    EIGSOL_CUDA(cudaMemcpyAsync(d, halo.peer_count.data(), sizeof(int64_t) * nranks, cudaMemcpyHostToDevice, c->stream));
-    EIGSOL_NCCL(nccl().GroupStart());
-    for (int q = 0; q < nranks; ++q) {
-        if (q == rank) continue;
-        EIGSOL_NCCL(nccl().Send(d + q, 1, ncclInt64, q, c->nccl_comm, c->stream));
-        EIGSOL_NCCL(nccl().Recv(d + nranks + q, 1, ncclInt64, q, c->nccl_comm, c->stream));
-    }
-    EIGSOL_NCCL(nccl().GroupEnd());
-    EIGSOL_CUDA(cudaMemcpyAsync(send_count.data(), d + nranks, sizeof(int64_t) * nranks, cudaMemcpyDeviceToHost, c->stream));
-    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
-    send_count[rank] = 0;
-    for (int q = 0; q < nranks; ++q) send_off[q + 1] = send_off[q] + send_count[q];
-    const int64_t total_send = send_off[nranks];
+    std::vector<int32_t> idx;  // what each peer reads from me (global columns), grouped by peer
+    int64_t total_send = 0;
+    if (c->local) {
+        // single process: every rank reads its peers' halo plans directly
+        c->local->exchange(rank, &halo, [&](const std::vector<const void*>& sl) {
+            for (int q = 0; q < nranks; ++q)
+                send_count[size_t(q)] = q == rank ? 0 : static_cast<const HaloPlan*>(sl[size_t(q)])->peer_count[size_t(rank)];
+            for (int q = 0; q < nranks; ++q) send_off[size_t(q) + 1] = send_off[size_t(q)] + send_count[size_t(q)];
+            total_send = send_off[size_t(nranks)];
+            idx.resize(size_t(total_send));
+            for (int q = 0; q < nranks; ++q) {
+                if (send_count[size_t(q)] == 0) continue;
+                const HaloPlan* hq = static_cast<const HaloPlan*>(sl[size_t(q)]);
+                std::copy_n(hq->cols.begin() + hq->peer_off[size_t(rank)], send_count[size_t(q)], idx.begin() + send_off[size_t(q)]);
+            }
+        });
+        d_send_idx.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(total_send, 1)));
+    } else {
+        int64_t* d = c->scratch.as<int64_t>();
+        // counts: d[0..P) = what I need from each peer, d[P..2P) = what each peer needs from me
+        EIGSOL_CUDA(cudaMemcpyAsync(d, halo.peer_count.data(), sizeof(int64_t) * nranks, cudaMemcpyHostToDevice, c->stream));
+        EIGSOL_NCCL(nccl().GroupStart());
+        for (int q = 0; q < nranks; ++q) {
+            if (q == rank) continue;
+            EIGSOL_NCCL(nccl().Send(d + q, 1, ncclInt64, q, c->nccl_comm, c->stream));
+            EIGSOL_NCCL(nccl().Recv(d + nranks + q, 1, ncclInt64, q, c->nccl_comm, c->stream));
+        }
+        EIGSOL_NCCL(nccl().GroupEnd());
+        EIGSOL_CUDA(cudaMemcpyAsync(send_count.data(), d + nranks, sizeof(int64_t) * nranks, cudaMemcpyDeviceToHost, c->stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
+        send_count[rank] = 0;
+        for (int q = 0; q < nranks; ++q) send_off[q + 1] = send_off[q] + send_count[q];
+        total_send = send_off[nranks];
 
-    DevBuf d_need;  // my halo columns (global), grouped by owner
-    d_need.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(nhalo, 1)));
-    d_need.upload(halo.cols.data(), sizeof(int32_t) * size_t(nhalo), c->stream);
-    d_send_idx.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(total_send, 1)));
-    EIGSOL_NCCL(nccl().GroupStart());
-    for (int q = 0; q < nranks; ++q) {
-        if (q == rank) continue;
-        if (halo.peer_count[q] > 0)
-            EIGSOL_NCCL(nccl().Send(d_need.as<int32_t>() + halo.peer_off[q], size_t(halo.peer_count[q]), ncclInt32, q,
-                                    c->nccl_comm, c->stream));
-        if (send_count[q] > 0)
-            EIGSOL_NCCL(nccl().Recv(d_send_idx.as<int32_t>() + send_off[q], size_t(send_count[q]), ncclInt32, q,
-                                    c->nccl_comm, c->stream));
+        DevBuf d_need;  // my halo columns (global), grouped by owner
+        d_need.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(nhalo, 1)));
+        d_need.upload(halo.cols.data(), sizeof(int32_t) * size_t(nhalo), c->stream);
+        d_send_idx.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(total_send, 1)));
+        EIGSOL_NCCL(nccl().GroupStart());
+        for (int q = 0; q < nranks; ++q) {
+            if (q == rank) continue;
+            if (halo.peer_count[q] > 0)
+                EIGSOL_NCCL(nccl().Send(d_need.as<int32_t>() + halo.peer_off[q], size_t(halo.peer_count[q]), ncclInt32, q,
+                                        c->nccl_comm, c->stream));
+            if (send_count[q] > 0)
+                EIGSOL_NCCL(nccl().Recv(d_send_idx.as<int32_t>() + send_off[q], size_t(send_count[q]), ncclInt32, q,
+                                        c->nccl_comm, c->stream));
+        }
+        EIGSOL_NCCL(nccl().GroupEnd());
+        idx.assign(size_t(total_send), 0);
+        if (total_send)
+            EIGSOL_CUDA(cudaMemcpyAsync(idx.data(), d_send_idx.p, sizeof(int32_t) * size_t(total_send), cudaMemcpyDeviceToHost,
+                                        c->stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
     }
-    EIGSOL_NCCL(nccl().GroupEnd());
-    std::vector<int32_t> idx(size_t(total_send), 0);
-    if (total_send)
-        EIGSOL_CUDA(cudaMemcpyAsync(idx.data(), d_send_idx.p, sizeof(int32_t) * size_t(total_send), cudaMemcpyDeviceToHost,
-                                    c->stream));
-    EIGSOL_CUDA(cudaStreamSynchronize(c->stream));
     // global -> local numbering; a contiguous ascending run is sent straight from the vector
     for (int q = 0; q < nranks; ++q) {
         bool contig = true;
@@ -350,7 +447,9 @@ void MatrixImpl::plan_exchange() {
 // MODE_SPLIT (NCCL send/recv + all-reduce) when IPC mapping is not possible on some rank.
 // -------------------------------------------------------------------------------------------------
 struct PeerBlob {
-    cudaIpcMemHandle_t buf[kRing], scal, flag;
+    cudaIpcMemHandle_t buf[kRing], scal, flag;  // process-per-GPU group: CUDA IPC handles
+    void *raw_buf[kRing], *raw_scal, *raw_flag; // single-process group: plain device pointers (peer access)
+    int device;
     int64_t halo_base;                 // nloc_pad: where the halo segment starts in the vector buffers
     int64_t peer_off[kMaxPeers + 1];   // offset of each owner's entries inside the halo segment
 };
@@ -359,22 +458,30 @@ void MatrixImpl::setup_peer() {
     xmode = nranks == 1 ? MODE_FUSED : MODE_SPLIT;
     if (nranks == 1) return;
     const char* want = std::getenv("EIGSOL_B200_EXCHANGE");
-    const bool force_nccl = want && std::string(want) == "nccl";
+    const bool local = comm->local != nullptr;
+    const bool force_nccl = !local && want && std::string(want) == "nccl";
     d_scal_in.alloc(sizeof(double) * kRing * kMaxPeers * 4);
-    d_flag_in.alloc(sizeof(unsigned long long) * kMaxPeers);
+    d_flag_in.alloc(sizeof(unsigned long long) * 2 * kMaxPeers);  // [0,8): trip flags, [8,16): gate flags
     PeerBlob mine;
     std::memset(&mine, 0, sizeof mine);
     int ok = (nranks <= kMaxPeers && !force_nccl) ? 1 : 0;
-    if (ok) {
+    if (ok && !local) {
         for (int b = 0; b < kRing; ++b) ok &= cudaIpcGetMemHandle(&mine.buf[b], buf[b].p) == cudaSuccess;
         ok &= cudaIpcGetMemHandle(&mine.scal, d_scal_in.p) == cudaSuccess;
         ok &= cudaIpcGetMemHandle(&mine.flag, d_flag_in.p) == cudaSuccess;
         cudaGetLastError();
     }
+    for (int b = 0; b < kRing; ++b) mine.raw_buf[b] = buf[b].p;
+    mine.raw_scal = d_scal_in.p;
+    mine.raw_flag = d_flag_in.p;
+    mine.device = device;
     mine.halo_base = nloc_pad;
     for (int q = 0; q <= nranks && q <= kMaxPeers; ++q) mine.peer_off[q] = halo.peer_off[q];
     ok = comm_min_int(comm, ok);
-    if (!ok) return;
+    if (!ok) {
+        if (local) throw DeviceError("powerMethod: device error: a single-process GPU group holds at most 8 devices");
+        return;
+    }
     const std::vector<char> all = comm_allgather_bytes(comm, &mine, sizeof mine);
     PeerArgs pa;
     std::memset(&pa, 0, sizeof pa);
@@ -382,6 +489,7 @@ void MatrixImpl::setup_peer() {
     pa.rank = rank;
     pa.scal_in = d_scal_in.as<double>();
     pa.flag_in = d_flag_in.as<unsigned long long>();
+    pa.gate_in = d_flag_in.as<unsigned long long>() + kMaxPeers;
     pa.send_idx = d_send_idx.as<int32_t>();
     pa.spin_limit = (long long)env_int("EIGSOL_B200_PEER_TIMEOUT_MS", 4000) * 2000000LL;  // ~2 GHz ticks
     const size_t es = size_t(ss());
@@ -392,20 +500,41 @@ void MatrixImpl::setup_peer() {
         std::memcpy(&pb, all.data() + sizeof(PeerBlob) * q, sizeof pb);
         void* rb[kRing] = {nullptr, nullptr, nullptr};
         void *rs = nullptr, *rf = nullptr;
-        auto open = [&](void** dst, const cudaIpcMemHandle_t& h) {
-            if (cudaIpcOpenMemHandle(dst, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        if (local) {
+            // same process: enable peer access once per device pair and use the peer's pointers as they are
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, device, pb.device) != cudaSuccess || !can) {
                 cudaGetLastError();
                 mapped = 0;
-                return;
+                break;
             }
-            ipc_opened.push_back(*dst);
-        };
-        for (int b = 0; b < kRing && mapped; ++b) open(&rb[b], pb.buf[b]);
-        if (mapped) open(&rs, pb.scal);
-        if (mapped) open(&rf, pb.flag);
-        if (!mapped) break;
+            const cudaError_t e = cudaDeviceEnablePeerAccess(pb.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                mapped = 0;
+                break;
+            }
+            cudaGetLastError();
+            for (int b = 0; b < kRing; ++b) rb[b] = pb.raw_buf[b];
+            rs = pb.raw_scal;
+            rf = pb.raw_flag;
+        } else {
+            auto open = [&](void** dst, const cudaIpcMemHandle_t& h) {
+                if (cudaIpcOpenMemHandle(dst, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    mapped = 0;
+                    return;
+                }
+                ipc_opened.push_back(*dst);
+            };
+            for (int b = 0; b < kRing && mapped; ++b) open(&rb[b], pb.buf[b]);
+            if (mapped) open(&rs, pb.scal);
+            if (mapped) open(&rf, pb.flag);
+            if (!mapped) break;
+        }
         pa.peer_scal[q] = static_cast<double*>(rs);
         pa.peer_flag[q] = static_cast<unsigned long long*>(rf) + rank;
+        pa.peer_gate[q] = static_cast<unsigned long long*>(rf) + kMaxPeers + rank;
         if (send_count[q] == 0) continue;
         const size_t dst_off = size_t(pb.halo_base + pb.peer_off[rank]) * es;
         if (send_contig[q]) {
@@ -424,6 +553,9 @@ void MatrixImpl::setup_peer() {
     if (!mapped) {
         for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
         ipc_opened.clear();
+        if (local)
+            throw DeviceError("powerMethod: device error: the GPUs of the group cannot access each other's memory "
+                              "(peer access); run with EIGSOL_B200_NGPU=1");
         return;
     }
     pa.debug_nowait = env_int("EIGSOL_B200_DEBUG_NOWAIT", 0);
@@ -431,6 +563,10 @@ void MatrixImpl::setup_peer() {
     for (int q = 0; q < nranks; ++q)
         if (q != rank && halo.peer_count[size_t(q)] > 0) pa.halo_src_mask |= 1u << q;
     if (env_int("EIGSOL_B200_DEBUG_NOSEND", 0)) pa.nsend = pa.nlist = 0;  // timing experiments only: results are wrong
+    if (env_int("EIGSOL_B200_PEER_STATS", 0)) {
+        d_stats.alloc(sizeof(unsigned long long) * kPeerStats);
+        pa.stats = d_stats.as<unsigned long long>();
+    }
     peer_h = pa;
     d_peer.alloc(sizeof(PeerArgs));
     EIGSOL_CUDA(cudaMemcpy(d_peer.p, &pa, sizeof pa, cudaMemcpyHostToDevice));
@@ -597,6 +733,176 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
 }
 
 // -------------------------------------------------------------------------------------------------
+// Single-process group, CSC input (what EigSol::Matrix holds): the P GPUs split the UPLOAD by column slabs
+// -- contiguous pieces of the caller's three arrays, 1/P of the bytes over each GPU's own PCIe link -- and the
+// ROWS by the same boundaries (row_begin == slab boundaries: nnz-balanced for a structurally symmetric matrix,
+// correct for any).  Every rank then pulls the entries of its rows out of every slab with peer loads over NVLink
+// (slab order = ascending columns), and transposes its COO piece to CSR with global columns on its own GPU;
+// finish_rows_on_device() does the rest.  row_begin must be set.
+// -------------------------------------------------------------------------------------------------
+struct SlabShow {
+    const int32_t *sinner, *scol;
+    const void* svals;
+    int64_t snnz;
+};
+
+void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                                       const void* values) {
+    Trace tr;
+    dense = false;
+    lo = row_begin[size_t(rank)];
+    hi = row_begin[size_t(rank) + 1];
+    nloc = hi - lo;
+    const int64_t c0 = lo, c1 = hi;  // my column slab
+    const int64_t e0 = outer[c0], e1 = outer[c1];
+    const int64_t snnz = e1 - e0, scols = c1 - c0;
+    const size_t s = size_t(ss());
+    const int B = 256;
+    DevBuf d_souter, d_sinner, d_svals, d_scol, d_flags;
+    d_flags.alloc(64);
+    d_souter.alloc(sizeof(int32_t) * size_t(scols + 1));
+    d_sinner.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(snnz, 1)));
+    d_scol.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(snnz, 1)));
+    d_svals.alloc(size_t(std::max<int64_t>(snnz, 1)) * s);
+    {
+        StagedUploader up;
+        up.add(d_souter.p, outer + c0, sizeof(int32_t) * size_t(scols + 1));
+        up.add(d_sinner.p, inner + e0, sizeof(int32_t) * size_t(snnz));
+        up.add(d_svals.p, static_cast<const char*>(values) + size_t(e0) * s, size_t(snnz) * s);
+        EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+    }
+    tr.mark("group csc: slab upload");
+    if (e0 != 0) rebase_kernel<<<unsigned((scols + 1 + B - 1) / B), B, 0, stream>>>(d_souter.as<int32_t>(), scols + 1, int32_t(e0));
+    if (snnz > 0)
+        slab_expand_kernel<<<unsigned((snnz + B - 1) / B), B, 0, stream>>>(d_souter.as<int32_t>(), d_sinner.as<int32_t>(), scols, c0,
+                                                                           rows, snnz, d_scol.as<int32_t>(), d_flags.as<int>());
+    launches += 2;
+    int hflags = 0;
+    EIGSOL_CUDA(cudaMemcpyAsync(&hflags, d_flags.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    int rows_ok = (hflags & 2) ? 0 : 1;
+    rows_ok = comm_min_int(comm, rows_ok);  // every rank takes the same exit
+    if (!rows_ok) throw PlanError("CSC inner index out of range");
+    // peer access to every slab
+    for (int q = 0; q < nranks; ++q) {
+        if (q == rank) continue;
+        int can = 0;
+        const int qdev = comm->local_devices[size_t(q)];
+        if (cudaDeviceCanAccessPeer(&can, device, qdev) != cudaSuccess || !can)
+            throw DeviceError("powerMethod: device error: the GPUs of the group cannot access each other's memory (peer access)");
+        const cudaError_t e = cudaDeviceEnablePeerAccess(qdev, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) EIGSOL_CUDA(e);
+        cudaGetLastError();
+    }
+    SlabShow mine{d_sinner.as<int32_t>(), d_scol.as<int32_t>(), d_svals.p, snnz};
+    const std::vector<char> all = comm_allgather_bytes(comm, &mine, sizeof mine);  // also the barrier: all slabs are resident
+    std::vector<SlabShow> slab{size_t(nranks), SlabShow{}};
+    std::memcpy(slab.data(), all.data(), all.size());
+    // 1. how many entries of each slab belong to my rows
+    DevBuf d_counts;
+    d_counts.alloc(sizeof(unsigned long long) * size_t(nranks));
+    int64_t max_snnz = 1;
+    for (int q = 0; q < nranks; ++q) {
+        max_snnz = std::max(max_snnz, slab[size_t(q)].snnz);
+        if (slab[size_t(q)].snnz == 0) continue;
+        const int g = int(std::min<int64_t>((slab[size_t(q)].snnz + B - 1) / B, int64_t(sm_count) * 8));
+        slab_count_kernel<<<g, B, 0, stream>>>(slab[size_t(q)].sinner, slab[size_t(q)].snnz, int32_t(lo), int32_t(hi),
+                                               d_counts.as<unsigned long long>() + q);
+        ++launches;
+    }
+    std::vector<unsigned long long> cnt(size_t(nranks), 0);
+    EIGSOL_CUDA(cudaMemcpyAsync(cnt.data(), d_counts.p, sizeof(unsigned long long) * size_t(nranks), cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    int64_t nnz = 0;
+    for (auto v : cnt) nnz += int64_t(v);
+    if (nnz > INT32_MAX) throw PlanError("a rank's row block holds more than 2^31-1 entries");
+    local_nnz = nnz;
+    tr.mark("group csc: expand + count");
+    // 2. pull them, slab by slab, into COO arrays (key = local row, global column, value)
+    const size_t nz = size_t(std::max<int64_t>(nnz, 1));
+    DevBuf d_key, d_col, d_val, d_iota, d_sel, d_nsel, d_tmp;
+    d_key.alloc(sizeof(int32_t) * nz);
+    d_col.alloc(sizeof(int32_t) * nz);
+    d_val.alloc(nz * s);
+    d_iota.alloc(sizeof(int32_t) * nz);
+    d_sel.alloc(sizeof(int32_t) * size_t(max_snnz));
+    d_nsel.alloc(sizeof(int));
+    d_rowptr.alloc(sizeof(int32_t) * size_t(nloc + 1));  // zero-filled: the row histogram
+    size_t tb = 0;
+    {
+        cub::CountingInputIterator<int32_t> it0(0);
+        EIGSOL_CUDA(cub::DeviceSelect::If(nullptr, tb, it0, d_sel.as<int32_t>(), d_nsel.as<int>(), int(max_snnz),
+                                          RowInRange{nullptr, 0, 0}, stream));
+    }
+    d_tmp.alloc(tb);
+    int64_t off = 0;
+    for (int q = 0; q < nranks; ++q) {
+        const int64_t nq = int64_t(cnt[size_t(q)]);
+        if (nq == 0) continue;
+        const SlabShow& sq = slab[size_t(q)];
+        cub::CountingInputIterator<int32_t> it0(0);
+        size_t tbq = tb;
+        EIGSOL_CUDA(cub::DeviceSelect::If(d_tmp.p, tbq, it0, d_sel.as<int32_t>(), d_nsel.as<int>(), int(sq.snnz),
+                                          RowInRange{sq.sinner, int32_t(lo), int32_t(hi)}, stream));
+        const unsigned g = unsigned((nq + B - 1) / B);
+        if (dtype)
+            slab_pull_kernel<double2><<<g, B, 0, stream>>>(d_sel.as<int32_t>(), nq, sq.sinner, sq.scol,
+                                                           static_cast<const double2*>(sq.svals), int32_t(lo),
+                                                           d_key.as<int32_t>() + off, d_col.as<int32_t>() + off,
+                                                           d_val.as<double2>() + off, d_iota.as<int32_t>() + off, int32_t(off),
+                                                           d_rowptr.as<int32_t>());
+        else
+            slab_pull_kernel<double><<<g, B, 0, stream>>>(d_sel.as<int32_t>(), nq, sq.sinner, sq.scol,
+                                                          static_cast<const double*>(sq.svals), int32_t(lo),
+                                                          d_key.as<int32_t>() + off, d_col.as<int32_t>() + off,
+                                                          d_val.as<double>() + off, d_iota.as<int32_t>() + off, int32_t(off),
+                                                          d_rowptr.as<int32_t>());
+        launches += 2;
+        off += nq;
+    }
+    EIGSOL_CUDA(cudaGetLastError());
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    comm->local->barrier();  // every rank has pulled: the slabs may go
+    d_souter.release();
+    d_sinner.release();
+    d_scol.release();
+    d_svals.release();
+    d_sel.release();
+    tr.mark("group csc: pull");
+    // 3. COO (column-major order) -> CSR: stable sort by local row keeps the columns ascending inside a row
+    d_colidx.alloc(sizeof(int32_t) * nz);
+    d_vals.alloc(nz * s);
+    if (nnz > 0) {
+        DevBuf d_perm, d_keys2, d_t1, d_t2;
+        d_perm.alloc(sizeof(int32_t) * nz);
+        d_keys2.alloc(sizeof(int32_t) * nz);
+        int end_bit = 1;
+        while (end_bit < 31 && (int64_t(1) << end_bit) < std::max<int64_t>(nloc, 2)) ++end_bit;
+        size_t t1 = 0, t2 = 0;
+        EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, t1, d_key.as<int32_t>(), d_keys2.as<int32_t>(), d_iota.as<int32_t>(),
+                                                    d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
+        d_t1.alloc(t1);
+        EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(d_t1.p, t1, d_key.as<int32_t>(), d_keys2.as<int32_t>(), d_iota.as<int32_t>(),
+                                                    d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, t2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(nloc + 1), stream));
+        d_t2.alloc(t2);
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(d_t2.p, t2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(nloc + 1), stream));
+        const unsigned gnz = unsigned((nnz + B - 1) / B);
+        if (dtype)
+            csc_gather_kernel<double2><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_val.as<double2>(), nnz,
+                                                              d_colidx.as<int32_t>(), d_vals.as<double2>());
+        else
+            csc_gather_kernel<double><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_val.as<double>(), nnz,
+                                                             d_colidx.as<int32_t>(), d_vals.as<double>());
+        launches += 3;
+        EIGSOL_CUDA(cudaGetLastError());
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    }
+    tr.mark("group csc: transpose");
+    finish_rows_on_device();
+}
+
+// -------------------------------------------------------------------------------------------------
 // Row block [lo, hi) in CSR with GLOBAL columns (each rank of a multi-GPU run, or the whole matrix on one
 // GPU): staged upload straight from the caller's arrays, then halo discovery, column renumbering and row
 // statistics on the device (ingest.cuh).  row_begin must be set.
@@ -609,10 +915,12 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     nloc = hi - lo;
     if (n > INT32_MAX) throw PlanError("matrix dimension exceeds int32 indices");
     if (!rowptr) throw PlanError("null rowptr");
-    if (rowptr[0] != 0) throw PlanError("CSR rowptr must start at 0");
+    // rowptr points at this rank's first row; a block cut out of a larger CSR array starts at base != 0
+    const int32_t base = rowptr[0];
+    if (base < 0) throw PlanError("CSR rowptr must start at 0");
     for (int64_t i = 0; i < nloc; ++i)
         if (rowptr[i + 1] < rowptr[i]) throw PlanError("CSR rowptr not monotone");
-    const int64_t nnz = rowptr[nloc];
+    const int64_t nnz = int64_t(rowptr[nloc]) - base;
     if (nnz > 0 && (!colidx || !values)) throw PlanError("null colidx");
     local_nnz = nnz;
     const size_t s = size_t(ss());
@@ -622,10 +930,23 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     d_vals.alloc(nz * s);
     StagedUploader up;
     up.add(d_rowptr.p, rowptr, sizeof(int32_t) * size_t(nloc + 1));
-    up.add(d_colidx.p, colidx, sizeof(int32_t) * size_t(nnz));
-    up.add(d_vals.p, values, size_t(nnz) * s);
+    up.add(d_colidx.p, colidx + base, sizeof(int32_t) * size_t(nnz));
+    up.add(d_vals.p, static_cast<const char*>(values) + size_t(base) * s, size_t(nnz) * s);
     EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+    if (base != 0) {
+        const unsigned g = unsigned((nloc + 1 + 255) / 256);
+        rebase_kernel<<<g, 256, 0, stream>>>(d_rowptr.as<int32_t>(), nloc + 1, base);
+        ++launches;
+    }
     tr.mark("rows(dev): staged upload");
+    finish_rows_on_device();
+}
+
+// The rank's rows are resident as CSR with GLOBAL columns (d_rowptr / d_colidx / d_vals, local_nnz set): halo
+// discovery, column renumbering, row statistics, exchange plan, kernel choice -- all on the device.
+void MatrixImpl::finish_rows_on_device() {
+    Trace tr;
+    const int64_t nnz = local_nnz;
     const int B = 256;
     const unsigned gnz = unsigned((std::max<int64_t>(nnz, 1) + B - 1) / B);
     const unsigned gn = unsigned((std::max<int64_t>(n, 1) + B - 1) / B);
@@ -767,7 +1088,8 @@ void MatrixImpl::compute_prescale() {
 
 void MatrixImpl::drop_graph() {
     if (graph) cudaGraphExecDestroy(graph);
-    graph = nullptr;
+    if (graph_short) cudaGraphExecDestroy(graph_short);
+    graph = graph_short = nullptr;
     graph_len = 0;
 }
 
@@ -1135,20 +1457,51 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol, bool unit_scale) 
                                     cudaMemcpyHostToDevice, stream));
     if (dense) EIGSOL_CUDA(cudaMemsetAsync(d_tile_ticket.p, 0, sizeof(unsigned) * size_t(ntiles), stream));
     if (nranks > 1) {
-        // x0 is global on every rank: the halo of launch 0 comes straight from it (no exchange needed)
+        // x0 is global on every rank: the halo of launch 0 comes straight from it (no exchange needed).  The halo
+        // columns are sorted, so a stencil's halo is a handful of contiguous runs: one copy per run; a scattered
+        // halo is gathered on the host first.
         if (nhalo) {
-            std::vector<char> hx(size_t(nhalo) * s);
             const char* src = static_cast<const char*>(x0);
-            for (int64_t k = 0; k < nhalo; ++k) std::memcpy(hx.data() + size_t(k) * s, src + size_t(halo.cols[k]) * s, s);
-            EIGSOL_CUDA(cudaMemcpyAsync(buf[0].as<char>() + size_t(nloc_pad) * s, hx.data(), hx.size(),
-                                        cudaMemcpyHostToDevice, stream));
-            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+            char* dst = buf[0].as<char>() + size_t(nloc_pad) * s;
+            std::vector<std::pair<int64_t, int64_t>> runs;  // {first halo slot, length}
+            for (int64_t k = 0; k < nhalo;) {
+                int64_t e = k + 1;
+                while (e < nhalo && halo.cols[size_t(e)] == halo.cols[size_t(e - 1)] + 1) ++e;
+                runs.emplace_back(k, e - k);
+                k = e;
+                if (runs.size() > 64) break;
+            }
+            if (runs.size() <= 64) {
+                for (const auto& r : runs)
+                    EIGSOL_CUDA(cudaMemcpyAsync(dst + size_t(r.first) * s, src + size_t(halo.cols[size_t(r.first)]) * s,
+                                                size_t(r.second) * s, cudaMemcpyHostToDevice, stream));
+            } else {
+                std::vector<char> hx(size_t(nhalo) * s);
+                for (int64_t k = 0; k < nhalo; ++k) std::memcpy(hx.data() + size_t(k) * s, src + size_t(halo.cols[size_t(k)]) * s, s);
+                EIGSOL_CUDA(cudaMemcpyAsync(dst, hx.data(), hx.size(), cudaMemcpyHostToDevice, stream));
+                EIGSOL_CUDA(cudaStreamSynchronize(stream));
+            }
         }
         // barrier: no rank may start launching (and storing into peers) before every rank has reset
-        EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 1, ncclDouble, ncclSum, comm->nccl_comm, stream));
+        rank_barrier();
     }
+    ensure_graphs();  // captured and instantiated here, never inside a timed batch of trips
     EIGSOL_CUDA(cudaStreamSynchronize(stream));  // x0 is a borrowed host pointer
     begun = true;
+}
+
+// Barrier of the ranks on the device timeline of `stream`: what is queued behind it starts on every rank within
+// microseconds of the last rank's arrival.  MODE_PEER: the gate kernel (flags in peer memory); NCCL: an all-reduce.
+void MatrixImpl::rank_barrier() {
+    if (nranks == 1) return;
+    if (xmode == MODE_PEER) {
+        ++gate_epoch;
+        peer_gate_kernel<<<1, 32, 0, stream>>>(d_peer.as<PeerArgs>(), gate_epoch, d_state.as<PowerState>());
+        ++launches;
+        EIGSOL_CUDA(cudaGetLastError());
+    } else {
+        EIGSOL_NCCL(nccl().AllReduce(d_scal.p, d_scal.p, 1, ncclDouble, ncclSum, comm->nccl_comm, stream));
+    }
 }
 
 // x exchange of the multi-GPU path: every rank sends the entries its peers' rows reference and
@@ -1187,37 +1540,62 @@ void MatrixImpl::exchange_halo(int in) {
     else exchange_impl<double>(*this, in);
 }
 
+// CUDA graphs of kGraphLong and kRing matvec launches (multiples of the ring length, so every node's ring phase is
+// a constant), with the programmatic-dependent-launch edges between the nodes.  Built once per launch
+// configuration, at begin() -- outside any timed region.
+void MatrixImpl::ensure_graphs() {
+    if (xmode == MODE_SPLIT) return;
+    int glen = env_int("EIGSOL_B200_GRAPH", 15);
+    glen = glen / kRing * kRing;
+    auto capture = [&](int len) {
+        cudaGraph_t g = nullptr;
+        cudaGraphExec_t ge = nullptr;
+        EIGSOL_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+        const int64_t keep = launches;
+        try {
+            for (int i = 0; i < len; ++i) launch_matvec(i % kRing);
+        } catch (...) {
+            cudaStreamEndCapture(stream, &g);
+            if (g) cudaGraphDestroy(g);
+            throw;
+        }
+        launches = keep;
+        EIGSOL_CUDA(cudaStreamEndCapture(stream, &g));
+        const cudaError_t e = cudaGraphInstantiate(&ge, g, 0);
+        cudaGraphDestroy(g);
+        EIGSOL_CUDA(e);
+        EIGSOL_CUDA(cudaGraphUpload(ge, stream));
+        return ge;
+    };
+    if (glen >= kRing && !graph_short) graph_short = capture(kRing);
+    if (glen > kRing && (!graph || graph_len != glen)) {
+        if (graph) cudaGraphExecDestroy(graph);
+        graph = capture(glen);
+        graph_len = glen;
+    }
+}
+
 void MatrixImpl::issue_trips(int k) {
     if (k <= 0) return;
     EIGSOL_CUDA(cudaSetDevice(device));
     if (xmode != MODE_SPLIT) {
-        // a CUDA graph of glen launches (a multiple of kRing, so every node's ring phase is fixed)
-        int glen = env_int("EIGSOL_B200_GRAPH", 15);
-        glen = glen / kRing * kRing;
-        while (k > 0 && (issued % kRing != 0 || k < glen || glen < kRing)) {
+        // single launches up to a ring boundary, then the long graph, then the 3-launch graph, then the rest
+        while (k > 0 && issued % kRing != 0) {
             launch_matvec(issued % kRing);
             ++issued;
             --k;
         }
-        if (k >= glen && glen >= kRing) {
-            if (!graph || graph_len != glen) {
-                drop_graph();
-                cudaGraph_t g = nullptr;
-                EIGSOL_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
-                const int64_t keep = launches;
-                for (int i = 0; i < glen; ++i) launch_matvec(i % kRing);
-                launches = keep;
-                EIGSOL_CUDA(cudaStreamEndCapture(stream, &g));
-                EIGSOL_CUDA(cudaGraphInstantiate(&graph, g, 0));
-                cudaGraphDestroy(g);
-                graph_len = glen;
-            }
-            while (k >= glen) {
-                EIGSOL_CUDA(cudaGraphLaunch(graph, stream));
-                launches += glen;
-                issued += glen;
-                k -= glen;
-            }
+        while (graph && k >= graph_len) {
+            EIGSOL_CUDA(cudaGraphLaunch(graph, stream));
+            launches += graph_len;
+            issued += graph_len;
+            k -= graph_len;
+        }
+        while (graph_short && k >= kRing) {
+            EIGSOL_CUDA(cudaGraphLaunch(graph_short, stream));
+            launches += kRing;
+            issued += kRing;
+            k -= kRing;
         }
         for (; k > 0; --k) {
             launch_matvec(issued % kRing);
@@ -1258,6 +1636,7 @@ void MatrixImpl::step(int trips, float* ms_out) {
     if (!begun) throw StateError("eigsol_b200_power_step called before eigsol_b200_power_begin");
     if (trips < 0) throw PlanError("negative trip count");
     EIGSOL_CUDA(cudaSetDevice(device));
+    rank_barrier();  // the ranks' timers start together, whatever the skew of their host threads
     EIGSOL_CUDA(cudaEventRecord(ev0, stream));
     issue_trips(trips);
     EIGSOL_CUDA(cudaEventRecord(ev1, stream));
@@ -1271,6 +1650,15 @@ void MatrixImpl::gather_download(const void* d_local, void* host_out) {
     if (nranks == 1) {
         if (n) EIGSOL_CUDA(cudaMemcpyAsync(host_out, d_local, size_t(n) * s, cudaMemcpyDeviceToHost, stream));
         EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        return;
+    }
+    if (comm->local) {
+        // single process: host_out is the SAME buffer on every rank; each writes its own rows
+        if (nloc)
+            EIGSOL_CUDA(cudaMemcpyAsync(static_cast<char*>(host_out) + size_t(lo) * s, d_local, size_t(nloc) * s,
+                                        cudaMemcpyDeviceToHost, stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        comm->local->barrier();  // the whole vector is in place when any rank returns
         return;
     }
     const size_t mul = s / sizeof(double);
@@ -1388,6 +1776,129 @@ void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
     info->kernels_per_trip = per_trip;
 }
 
+// -------------------------------------------------------------------------------------------------
+// Single-process multi-GPU group behind ONE matrix handle (SURVEY.md 8e "Process model"; EIGSOL_B200_NGPU=P):
+// P persistent host threads, one per device, each driving one rank (MatrixImpl) exactly as a process-per-GPU
+// rank would -- the same partition, the same fused peer-memory kernel -- so that the reference-facing call
+// EigSol::powerMethod(M, opts) shards over the GPUs of the box without the caller knowing.
+// -------------------------------------------------------------------------------------------------
+struct LocalSolver {
+    const int P;
+    LocalGroup group;
+    std::vector<int> devices;
+    std::vector<std::unique_ptr<Comm>> comms;
+    std::vector<std::unique_ptr<MatrixImpl>> ranks;
+    std::vector<std::thread> threads;
+    std::mutex mu;
+    std::condition_variable cv_work, cv_done;
+    std::function<void(int)> job;
+    uint64_t job_id = 0;
+    int pending = 0;
+    bool quit = false;
+    std::vector<std::exception_ptr> errors;
+    std::vector<uint64_t> error_seq;
+    uint64_t seq = 0;
+
+    LocalSolver(int nranks, int first_device) : P(nranks), group(nranks) {
+        for (int r = 0; r < P; ++r) devices.push_back(first_device + r);
+        comms.resize(size_t(P));
+        ranks.resize(size_t(P));
+        errors.resize(size_t(P));
+        error_seq.assign(size_t(P), 0);
+        for (int r = 0; r < P; ++r) threads.emplace_back([this, r] { worker(r); });
+        run_all([this](int r) {
+            std::unique_ptr<Comm> c(new Comm);
+            c->rank = r;
+            c->nranks = P;
+            c->device = devices[size_t(r)];
+            c->local = &group;
+            c->local_devices = devices;
+            EIGSOL_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+            comms[size_t(r)] = std::move(c);
+            ranks[size_t(r)].reset(new MatrixImpl);
+        });
+    }
+    ~LocalSolver() {
+        try {
+            run_all([this](int r) {
+                ranks[size_t(r)].reset();
+                comms[size_t(r)].reset();
+            });
+        } catch (...) {
+        }
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            quit = true;
+        }
+        cv_work.notify_all();
+        for (auto& t : threads) t.join();
+    }
+    void worker(int r) {
+        cudaSetDevice(devices[size_t(r)]);
+        uint64_t seen = 0;
+        for (;;) {
+            std::function<void(int)> fn;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv_work.wait(lk, [&] { return quit || job_id != seen; });
+                if (quit) return;
+                seen = job_id;
+                fn = job;
+            }
+            std::exception_ptr err;
+            try {
+                fn(r);
+            } catch (...) {
+                err = std::current_exception();
+                group.fail();  // peers blocked in a barrier leave it with an exception instead of waiting forever
+            }
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                if (err) {
+                    errors[size_t(r)] = err;
+                    error_seq[size_t(r)] = ++seq;
+                }
+                if (--pending == 0) cv_done.notify_all();
+            }
+        }
+    }
+    // runs fn(rank) on every rank's thread; rethrows the FIRST failure (the later ones are its echoes)
+    void run_all(std::function<void(int)> fn) {
+        std::unique_lock<std::mutex> lk(mu);
+        for (auto& e : errors) e = nullptr;
+        seq = 0;
+        job = std::move(fn);
+        pending = P;
+        ++job_id;
+        cv_work.notify_all();
+        cv_done.wait(lk, [&] { return pending == 0; });
+        int first = -1;
+        for (int r = 0; r < P; ++r)
+            if (errors[size_t(r)] && (first < 0 || error_seq[size_t(r)] < error_seq[size_t(first)])) first = r;
+        if (first >= 0) {
+            group.reset();
+            std::rethrow_exception(errors[size_t(first)]);
+        }
+    }
+    MatrixImpl& r0() { return *ranks[0]; }
+};
+
+// GPUs a comm == NULL matrix is sharded over: EIGSOL_B200_NGPU (default 1), at most the visible devices, at most 8,
+// and no more than one GPU per EIGSOL_B200_MIN_ROWS_PER_GPU rows (default 1024): tiny matrices stay on one GPU.
+static int group_size_for(int64_t n) {
+    int want = env_int("EIGSOL_B200_NGPU", 1);
+    if (want <= 1) return 1;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess) {
+        cudaGetLastError();
+        return 1;
+    }
+    want = std::min({want, ndev, kMaxPeers});
+    const int64_t per = std::max(1, env_int("EIGSOL_B200_MIN_ROWS_PER_GPU", 1024));
+    want = int(std::min<int64_t>(want, std::max<int64_t>(1, n / per)));
+    return std::max(want, 1);
+}
+
 }  // namespace eigsol_b200
 
 #include "block_host.cuh"
@@ -1397,16 +1908,25 @@ void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
 // =================================================================================================
 using namespace eigsol_b200;
 
+// One handle = one rank (a single GPU, or one rank of a process-per-GPU group) or a whole single-process group.
 struct eigsol_b200_matrix {
-    MatrixImpl impl;
+    std::unique_ptr<MatrixImpl> one;
+    std::unique_ptr<LocalSolver> group;
+    std::mutex mu;  // calls on ONE handle are serialised; different handles (e.g. the ranks of a thread-per-GPU
+                    // group) run concurrently
+    MatrixImpl& lead() { return group ? group->r0() : *one; }
+    const MatrixImpl& lead() const { return group ? *group->ranks[0] : *one; }
+    // runs f(rank impl) on the handle's rank(s)
+    template <class F> void each(F&& f) {
+        if (group) group->run_all([&](int r) { f(*group->ranks[size_t(r)], r); });
+        else f(*one, 0);
+    }
 };
 struct eigsol_b200_comm {
     Comm impl;
 };
 
 namespace {
-std::mutex g_api_mutex;  // calls are serialised (SURVEY.md 8b "Threading")
-
 template <class F> int guarded(F&& f) {
     try {
         g_last_error.clear();
@@ -1449,6 +1969,19 @@ int check_dtype(int dtype) {
         return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: dtype must be 0 (f64) or 1 (c128)");
     return EIGSOL_B200_OK;
 }
+
+// comm == NULL and EIGSOL_B200_NGPU > 1: the handle becomes a single-process group over the first P devices
+// (counted from the calling thread's current device)
+std::unique_ptr<LocalSolver> make_group(int64_t n) {
+    require_device();
+    const int P = group_size_for(n);
+    if (P <= 1) return nullptr;
+    int dev0 = 0, ndev = 0;
+    EIGSOL_CUDA(cudaGetDevice(&dev0));
+    EIGSOL_CUDA(cudaGetDeviceCount(&ndev));
+    if (dev0 + P > ndev) dev0 = 0;
+    return std::unique_ptr<LocalSolver>(new LocalSolver(P, dev0));
+}
 }  // namespace
 
 extern "C" {
@@ -1464,7 +1997,7 @@ int eigsol_b200_device_count(void) {
     return n;
 }
 
-const char* eigsol_b200_version(void) { return "eigsol_b200 0.1 (sm_100a)"; }
+const char* eigsol_b200_version(void) { return "eigsol_b200 0.2 (sm_100a)"; }
 
 int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
                                   const void* values, eigsol_b200_comm* comm, eigsol_b200_matrix** out) {
@@ -1472,16 +2005,34 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
     *out = nullptr;
     if (int e = check_dtype(dtype)) return e;
     if (int e = check_shape(rows, cols)) return e;
-    std::lock_guard<std::mutex> lock(g_api_mutex);
     return guarded([&] {
         if (!outer || (outer[cols] > 0 && (!inner || !values))) throw PlanError("null CSC array");
         std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
-        MatrixImpl& m = h->impl;
+        if (!comm) h->group = make_group(rows);
+        if (h->group) {
+            // column-slab boundaries from the column prefix `outer` (nnz-balanced), reused as the row partition
+            if (outer[0] != 0) throw PlanError("CSC outer index must start at 0 (compressed storage expected)");
+            for (int64_t j = 0; j < cols; ++j)
+                if (outer[j + 1] < outer[j]) throw PlanError("CSC outer index not monotone");
+            const std::vector<int64_t> rb = partition_rows(cols, outer, h->group->P);
+            h->each([&](MatrixImpl& m, int r) {
+                m.init_common(dtype, h->group->comms[size_t(r)].get());
+                m.n = rows;
+                m.row_begin = rb;
+                m.init_sparse_group_csc(rows, cols, outer, inner, values);
+            });
+            *out = h.release();
+            ++g_matrices_created;
+            return int(EIGSOL_B200_OK);
+        }
+        h->one.reset(new MatrixImpl);
+        MatrixImpl& m = *h->one;
         m.init_common(dtype, comm ? &comm->impl : nullptr);
         m.n = rows;
         if (m.nranks == 1 && env_int("EIGSOL_B200_DEVICE_INGEST", 1)) {
             m.init_sparse_device_csc(rows, cols, outer, inner, values);
             *out = h.release();
+            ++g_matrices_created;
             return int(EIGSOL_B200_OK);
         }
         CsrHost g = csc_to_csr(dtype, rows, cols, outer, inner, values);
@@ -1503,6 +2054,7 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
             m.init_sparse_local(std::move(loc));
         }
         *out = h.release();
+        ++g_matrices_created;
         return int(EIGSOL_B200_OK);
     });
 }
@@ -1514,16 +2066,32 @@ int eigsol_b200_matrix_create_csr_rows(int dtype, int64_t n, int64_t row_begin, 
     *out = nullptr;
     if (int e = check_dtype(dtype)) return e;
     if (int e = check_shape(n, n)) return e;
-    std::lock_guard<std::mutex> lock(g_api_mutex);
     return guarded([&] {
         validate_csr_rows(n, row_count, rowptr, colidx);
         if (rowptr[row_count] > 0 && !values) throw PlanError("null values array");
         std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
-        MatrixImpl& m = h->impl;
+        if (!comm) {
+            if (row_begin != 0 || row_count != n) throw PlanError("without a comm the row block must be the whole matrix");
+            h->group = make_group(n);
+        }
+        if (h->group) {
+            // nnz-balanced row blocks; every rank uploads its own block straight from the caller's arrays
+            const std::vector<int64_t> rb = partition_rows(n, rowptr, h->group->P);
+            h->each([&](MatrixImpl& m, int r) {
+                m.init_common(dtype, h->group->comms[size_t(r)].get());
+                m.n = n;
+                m.row_begin = rb;
+                m.init_sparse_device_rows(rowptr + rb[size_t(r)], colidx, values);
+            });
+            *out = h.release();
+            ++g_matrices_created;
+            return int(EIGSOL_B200_OK);
+        }
+        h->one.reset(new MatrixImpl);
+        MatrixImpl& m = *h->one;
         m.init_common(dtype, comm ? &comm->impl : nullptr);
         m.n = n;
         if (m.nranks == 1) {
-            if (row_begin != 0 || row_count != n) throw PlanError("without a comm the row block must be the whole matrix");
             m.row_begin = {0, n};
         } else {
             const std::vector<int64_t> begins = comm_allgather_i64(m.comm, row_begin);
@@ -1537,6 +2105,7 @@ int eigsol_b200_matrix_create_csr_rows(int dtype, int64_t n, int64_t row_begin, 
         if (env_int("EIGSOL_B200_DEVICE_INGEST", 1)) {
             m.init_sparse_device_rows(rowptr, colidx, values);
             *out = h.release();
+            ++g_matrices_created;
             return int(EIGSOL_B200_OK);
         }
         CsrHost loc;
@@ -1549,6 +2118,7 @@ int eigsol_b200_matrix_create_csr_rows(int dtype, int64_t n, int64_t row_begin, 
         loc.vals.assign(static_cast<const double*>(values), static_cast<const double*>(values) + nnz * loc.spd());
         m.init_sparse_local(std::move(loc));
         *out = h.release();
+        ++g_matrices_created;
         return int(EIGSOL_B200_OK);
     });
 }
@@ -1561,22 +2131,24 @@ int eigsol_b200_matrix_create_dense(int dtype, int64_t rows, int64_t cols, const
     if (int e = check_shape(rows, cols)) return e;
     if (!a || lda < rows) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: bad dense matrix pointer / lda");
     if (rows > INT32_MAX / 2) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: dense order too large");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
     return guarded([&] {
         std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
-        MatrixImpl& m = h->impl;
-        m.init_common(dtype, comm ? &comm->impl : nullptr);
-        m.init_dense(rows, a, lda);
+        if (!comm) h->group = make_group(rows);
+        if (!h->group) h->one.reset(new MatrixImpl);
+        h->each([&](MatrixImpl& m, int r) {
+            m.init_common(dtype, h->group ? h->group->comms[size_t(r)].get() : (comm ? &comm->impl : nullptr));
+            m.init_dense(rows, a, lda);
+        });
         *out = h.release();
+        ++g_matrices_created;
         return int(EIGSOL_B200_OK);
     });
 }
 
 int eigsol_b200_matrix_destroy(eigsol_b200_matrix* m) {
     if (!m) return EIGSOL_B200_OK;
-    std::lock_guard<std::mutex> lock(g_api_mutex);
     return guarded([&] {
-        cudaSetDevice(m->impl.device);
+        if (m->one) cudaSetDevice(m->one->device);
         delete m;
         return int(EIGSOL_B200_OK);
     });
@@ -1584,17 +2156,30 @@ int eigsol_b200_matrix_destroy(eigsol_b200_matrix* m) {
 
 int eigsol_b200_matrix_get_info(const eigsol_b200_matrix* m, eigsol_b200_matrix_info* info) {
     if (!m || !info) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle / info");
-    m->impl.fill_info(info);
+    m->lead().fill_info(info);
+    if (m->group) {
+        // a single-process group reports rank 0's launch geometry and the LARGEST per-rank byte counts (the rank that
+        // bounds a trip)
+        for (const auto& r : m->group->ranks) {
+            eigsol_b200_matrix_info ri;
+            r->fill_info(&ri);
+            info->alg_bytes = std::max(info->alg_bytes, ri.alg_bytes);
+            info->stored_bytes = std::max(info->stored_bytes, ri.stored_bytes);
+            info->halo = std::max(info->halo, ri.halo);
+        }
+    }
     return EIGSOL_B200_OK;
 }
 
 int eigsol_b200_matrix_set_kernel(eigsol_b200_matrix* m, int kernel, int lanes) {
     if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        EIGSOL_CUDA(cudaSetDevice(m->impl.device));
-        m->impl.begun = false;
-        m->impl.set_kernel(kernel, lanes);
+        m->each([&](MatrixImpl& r, int) {
+            EIGSOL_CUDA(cudaSetDevice(r.device));
+            r.begun = false;
+            r.set_kernel(kernel, lanes);
+        });
         return int(EIGSOL_B200_OK);
     });
 }
@@ -1602,27 +2187,33 @@ int eigsol_b200_matrix_set_kernel(eigsol_b200_matrix* m, int kernel, int lanes) 
 int eigsol_b200_power_run(eigsol_b200_matrix* m, const void* x0, int max_iterations, double tolerance, void* x_out,
                           double lambda_out[2], int* iterations_out, int* converged_out) {
     if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        m->impl.run(x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
+        m->each([&](MatrixImpl& r, int k) {
+            // every rank of a group writes its own rows of x_out; the scalars come from rank 0 (identical everywhere)
+            r.run(x0, max_iterations, tolerance, x_out, k == 0 ? lambda_out : nullptr, k == 0 ? iterations_out : nullptr,
+                  k == 0 ? converged_out : nullptr);
+        });
         return int(EIGSOL_B200_OK);
     });
 }
 
 int eigsol_b200_power_begin(eigsol_b200_matrix* m, const void* x0, int max_iterations, double tolerance) {
     if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        m->impl.begin(x0, max_iterations, tolerance);
+        m->each([&](MatrixImpl& r, int) { r.begin(x0, max_iterations, tolerance); });
         return int(EIGSOL_B200_OK);
     });
 }
 
 int eigsol_b200_power_step(eigsol_b200_matrix* m, int trips, float* ms_out) {
     if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        m->impl.step(trips, ms_out);
+        float ms[kMaxPeers] = {};
+        m->each([&](MatrixImpl& r, int k) { r.step(trips, &ms[k]); });
+        if (ms_out) *ms_out = *std::max_element(ms, ms + kMaxPeers);  // a group: the slowest rank
         return int(EIGSOL_B200_OK);
     });
 }
@@ -1630,33 +2221,35 @@ int eigsol_b200_power_step(eigsol_b200_matrix* m, int trips, float* ms_out) {
 int eigsol_b200_power_end(eigsol_b200_matrix* m, void* x_out, double lambda_out[2], int* iterations_out,
                           int* converged_out) {
     if (!m) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null handle");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        m->impl.end(x_out, lambda_out, iterations_out, converged_out);
+        m->each([&](MatrixImpl& r, int k) {
+            r.end(x_out, k == 0 ? lambda_out : nullptr, k == 0 ? iterations_out : nullptr, k == 0 ? converged_out : nullptr);
+        });
         return int(EIGSOL_B200_OK);
     });
 }
 
 int eigsol_b200_matvec(eigsol_b200_matrix* m, const void* x, void* y) {
     if (!m || !x || !y) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        m->impl.matvec(x, y);
+        m->each([&](MatrixImpl& r, int) { r.matvec(x, y); });
         return int(EIGSOL_B200_OK);
     });
 }
 
 int eigsol_b200_rayleigh(eigsol_b200_matrix* m, const void* x, double dot_out[2], double* norm2_out) {
     if (!m || !x) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        double o[4];
-        m->impl.rayleigh(x, o);
+        double o[kMaxPeers][4] = {};
+        m->each([&](MatrixImpl& r, int k) { r.rayleigh(x, o[k]); });
         if (dot_out) {
-            dot_out[0] = o[0];
-            dot_out[1] = o[1];
+            dot_out[0] = o[0][0];
+            dot_out[1] = o[0][1];
         }
-        if (norm2_out) *norm2_out = o[2];
+        if (norm2_out) *norm2_out = o[0][2];
         return int(EIGSOL_B200_OK);
     });
 }
@@ -1665,10 +2258,11 @@ int eigsol_b200_block_power_run(eigsol_b200_matrix* m, int block, int nev, const
                                 double tolerance, void* x_out, double* lambda_out, int* iterations_out,
                                 int* converged_out, int* breakdown_out, float* ms_out) {
     if (!m || !x0 || !lambda_out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
-    std::lock_guard<std::mutex> lock(g_api_mutex);
+    std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
+        if (m->group) throw PlanError("the block power iteration runs on one GPU in this version (EIGSOL_B200_NGPU=1)");
         BlockResult r;
-        block_power_run(m->impl, block, nev, x0, max_iterations, tolerance, x_out, lambda_out, r);
+        block_power_run(*m->one, block, nev, x0, max_iterations, tolerance, x_out, lambda_out, r);
         if (iterations_out) *iterations_out = r.iterations;
         if (converged_out) *converged_out = r.converged;
         if (breakdown_out) *breakdown_out = r.breakdown;
@@ -1677,9 +2271,84 @@ int eigsol_b200_block_power_run(eigsol_b200_matrix* m, int block, int nev, const
     });
 }
 
-int64_t eigsol_b200_matrix_launch_count(const eigsol_b200_matrix* m) { return m ? m->impl.launches : 0; }
+int64_t eigsol_b200_matrices_created(void) { return g_matrices_created.load(); }
+
+int64_t eigsol_b200_matrix_launch_count(const eigsol_b200_matrix* m) {
+    if (!m) return 0;
+    if (!m->group) return m->one->launches;
+    int64_t total = 0;
+    for (const auto& r : m->group->ranks) total += r->launches;
+    return total;
+}
+
+// EIGSOL_B200_PEER_STATS=1: where the multi-GPU trips of this rank waited since the last call (kernels.cuh, PeerArgs::stats)
+int eigsol_b200_matrix_peer_stats(eigsol_b200_matrix* m, uint64_t out[8]) {
+    if (!m || !out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
+    std::lock_guard<std::mutex> lock(m->mu);
+    return guarded([&] {
+        std::memset(out, 0, sizeof(uint64_t) * 8);
+        MatrixImpl& r = m->lead();
+        if (!r.d_stats.p) return int(EIGSOL_B200_OK);
+        EIGSOL_CUDA(cudaSetDevice(r.device));
+        EIGSOL_CUDA(cudaStreamSynchronize(r.stream));
+        EIGSOL_CUDA(cudaMemcpy(out, r.d_stats.p, sizeof(uint64_t) * kPeerStats, cudaMemcpyDeviceToHost));
+        EIGSOL_CUDA(cudaMemset(r.d_stats.p, 0, sizeof(uint64_t) * kPeerStats));
+        return int(EIGSOL_B200_OK);
+    });
+}
 
 }  // extern "C"
+
+// ---- measurement: HBM ceiling of a read-dominated stream (probe.cuh) -------------------------------------
+extern "C" int eigsol_b200_hbm_probe(int64_t plane_bytes, int planes, int reps, double* best_gbps, double* mean_gbps) {
+    if (plane_bytes < 4096 || reps < 1 || (planes != 1 && planes != 4 && planes != 8 && planes != 12))
+        return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: hbm probe takes 1, 4, 8 or 12 read planes");
+    return guarded([&] {
+        require_device();
+        const int64_t n2 = plane_bytes / 16;
+        DevBuf in, out;
+        in.alloc(size_t(n2) * 16 * size_t(planes));
+        out.alloc(size_t(n2) * 16);
+        int dev = 0, sms = 148;
+        EIGSOL_CUDA(cudaGetDevice(&dev));
+        EIGSOL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        cudaStream_t st;
+        EIGSOL_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        cudaEvent_t e0, e1;
+        EIGSOL_CUDA(cudaEventCreate(&e0));
+        EIGSOL_CUDA(cudaEventCreate(&e1));
+        const int grid = sms * 8;
+        auto launch = [&] {
+            switch (planes) {
+                case 1: read_mix_kernel<1><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
+                case 4: read_mix_kernel<4><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
+                case 8: read_mix_kernel<8><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
+                default: read_mix_kernel<12><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
+            }
+        };
+        for (int w = 0; w < 3; ++w) launch();
+        double best = 0.0, sum = 0.0;
+        const double bytes = double(n2) * 16.0 * double(planes + 1);
+        for (int r = 0; r < reps; ++r) {
+            EIGSOL_CUDA(cudaEventRecord(e0, st));
+            launch();
+            EIGSOL_CUDA(cudaEventRecord(e1, st));
+            EIGSOL_CUDA(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            EIGSOL_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            const double g = bytes / (double(ms) * 1e-3) / 1e9;
+            best = std::max(best, g);
+            sum += g;
+        }
+        EIGSOL_CUDA(cudaGetLastError());
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaStreamDestroy(st);
+        if (best_gbps) *best_gbps = best;
+        if (mean_gbps) *mean_gbps = sum / reps;
+        return int(EIGSOL_B200_OK);
+    });
+}
 
 // ---- one-shot entry points ------------------------------------------------------------------------
 extern "C" {

@@ -18,8 +18,11 @@
 
 #include <atomic>
 #include <cstring>
+#include <mutex>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
 #include <thread>
 #include <vector>
 
@@ -28,27 +31,43 @@
 namespace eigsol_b200 {
 
 // ---- host -> device copy of a large pageable array through pinned staging, several threads ----------
-// Pinned staging buffers live for the life of the process (cudaHostAlloc costs milliseconds): slot t
-// belongs to uploader thread t.  Callers are serialised by the API mutex.
+// Pinned staging buffers live for the life of the process (cudaHostAlloc costs milliseconds).  Uploads of different
+// handles / ranks may run concurrently, so buffers are handed out and taken back under a lock.
 struct PinnedPool {
-    static constexpr int kMaxThreads = 16;
-    void* buf[kMaxThreads][2] = {};
+    static constexpr size_t kBytes = size_t(16) << 20;
+    static constexpr size_t kKeep = 64;  // at most 1 GB of pinned staging is kept
+    std::mutex mu;
+    std::vector<void*> idle;
     static PinnedPool& get() {
         static PinnedPool p;
         return p;
     }
-    cudaError_t ensure(int t, size_t bytes) {
-        for (int b = 0; b < 2; ++b)
-            if (!buf[t][b]) {
-                const cudaError_t e = cudaHostAlloc(&buf[t][b], bytes, cudaHostAllocDefault);
-                if (e != cudaSuccess) return e;
+    cudaError_t acquire(void** out) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            if (!idle.empty()) {
+                *out = idle.back();
+                idle.pop_back();
+                return cudaSuccess;
             }
-        return cudaSuccess;
+        }
+        return cudaHostAlloc(out, kBytes, cudaHostAllocPortable);
+    }
+    void release(void* p) {
+        if (!p) return;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            if (idle.size() < kKeep) {
+                idle.push_back(p);
+                return;
+            }
+        }
+        cudaFreeHost(p);
     }
 };
 
 struct StagedUploader {
-    static constexpr size_t kChunk = size_t(16) << 20;
+    static constexpr size_t kChunk = PinnedPool::kBytes;
     struct Job {
         char* dst;
         const char* src;
@@ -64,19 +83,18 @@ struct StagedUploader {
     cudaError_t run(int device, int nthreads) {
         if (jobs.empty()) return cudaSuccess;
         nthreads = int(std::max<size_t>(1, std::min<size_t>(size_t(nthreads), jobs.size())));
-        nthreads = std::min(nthreads, int(PinnedPool::kMaxThreads));
+        nthreads = std::min(nthreads, 16);
         std::atomic<size_t> next{0};
         std::atomic<int> err{int(cudaSuccess)};
-        auto worker = [&](int tid) {
+        auto worker = [&](int) {
             cudaSetDevice(device);
             void* pin[2] = {nullptr, nullptr};
             cudaStream_t st = nullptr;
             cudaEvent_t ev[2] = {nullptr, nullptr};
             cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
-            if (e == cudaSuccess) e = PinnedPool::get().ensure(tid, kChunk);
             for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
-                pin[b] = PinnedPool::get().buf[tid][b];
-                e = cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming);
+                e = PinnedPool::get().acquire(&pin[b]);
+                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming);
             }
             int b = 0;
             bool used[2] = {false, false};
@@ -95,8 +113,10 @@ struct StagedUploader {
                 const cudaError_t e2 = cudaStreamSynchronize(st);
                 if (e == cudaSuccess) e = e2;
             }
-            for (int k = 0; k < 2; ++k)
+            for (int k = 0; k < 2; ++k) {
                 if (ev[k]) cudaEventDestroy(ev[k]);
+                PinnedPool::get().release(pin[k]);
+            }
             if (st) cudaStreamDestroy(st);
             if (e != cudaSuccess) err.store(int(e));
         };
@@ -166,6 +186,69 @@ __global__ void row_stats_kernel(const int32_t* __restrict__ rowptr, int64_t row
     atomicMin(imin, mn);
     atomicAdd(padded, (unsigned long long)mx * 64ull);
     atomicAdd(var, v);
+}
+
+// ---- single-process group, CSC input: every GPU uploads one column slab; each rank then pulls the entries of
+// ---- ITS rows out of every slab over NVLink (peer loads), in slab order = ascending columns
+// Global column of every entry of a column slab (outer rebased to the slab: souter[0] == 0) + range check of rows.
+__global__ void slab_expand_kernel(const int32_t* __restrict__ souter, const int32_t* __restrict__ sinner, int64_t scols,
+                                   int64_t col0, int64_t rows, int64_t snnz, int32_t* __restrict__ scol, int* flags) {
+    const int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (p >= snnz) return;
+    int64_t lo = 0, hi = scols;  // largest j with souter[j] <= p
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(souter + mid) <= p) lo = mid;
+        else hi = mid;
+    }
+    scol[p] = int32_t(col0 + lo);
+    const int32_t r = sinner[p];
+    if (r < 0 || r >= rows) atomicOr(flags, 2);
+}
+
+// number of entries of a (peer's) slab whose row lies in [lo, hi)
+__global__ void slab_count_kernel(const int32_t* __restrict__ sinner, int64_t snnz, int32_t lo, int32_t hi,
+                                  unsigned long long* count) {
+    unsigned long long c = 0;
+    for (int64_t p = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; p < snnz; p += int64_t(gridDim.x) * blockDim.x) {
+        const int32_t r = sinner[p];
+        c += (r >= lo && r < hi) ? 1ull : 0ull;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) c += __shfl_down_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
+
+struct RowInRange {
+    const int32_t* sinner;
+    int32_t lo, hi;
+    __device__ __forceinline__ bool operator()(int32_t p) const {
+        const int32_t r = sinner[p];
+        return r >= lo && r < hi;
+    }
+};
+
+// copies the selected entries of a (peer's) slab into this rank's COO arrays: key = row - lo, global column, value
+template <class S>
+__global__ void slab_pull_kernel(const int32_t* __restrict__ sel, int64_t nsel, const int32_t* __restrict__ sinner,
+                                 const int32_t* __restrict__ scol, const S* __restrict__ svals, int32_t lo,
+                                 int32_t* __restrict__ key, int32_t* __restrict__ col, S* __restrict__ val,
+                                 int32_t* __restrict__ iota, int32_t iota0, int32_t* __restrict__ rowcount) {
+    const int64_t k = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (k >= nsel) return;
+    const int32_t p = sel[k];
+    const int32_t r = sinner[p] - lo;
+    key[k] = r;
+    col[k] = scol[p];
+    val[k] = svals[p];
+    iota[k] = iota0 + int32_t(k);
+    atomicAdd(rowcount + r, 1);
+}
+
+// rowptr of a row block cut out of a larger CSR array: make it start at 0
+__global__ void rebase_kernel(int32_t* __restrict__ rowptr, int64_t count, int32_t base) {
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < count) rowptr[i] -= base;
 }
 
 // ---- row-block ingest (multi-GPU: each rank holds rows [lo, hi) in CSR with GLOBAL columns) ----------

@@ -323,7 +323,17 @@ struct PeerArgs {
     long long spin_limit;             // clock64 ticks before a wait gives up (error -> STOP_ERROR)
     int debug_nowait;                 // timing experiments only: waits return at once (results are wrong)
     unsigned halo_src_mask;           // ranks that own halo entries of this rank (the ones a matvec warp waits for)
+    // device-side barrier of the ranks (peer_gate_kernel): gate_in[q] = last gate epoch rank q has entered
+    unsigned long long* gate_in;               // local [kMaxPeers]
+    unsigned long long* peer_gate[kMaxPeers];  // remote &gate_in[rank] of rank q
+    // EIGSOL_B200_PEER_STATS=1: where a multi-GPU trip waits (nanoseconds of %globaltimer), else nullptr
+    //   [0] control CTA: ns between publishing the flag and having every peer's flag, summed   [1] launches counted
+    //   [2] matvec warps that found the halo flag missing: ns spun, summed                     [3] such warps
+    //   [4] the longest single halo wait                [5] matvec warps that reached a halo unit (waited or not)
+    unsigned long long* stats;
 };
+
+constexpr int kPeerStats = 8;
 
 // Everything a matvec launch needs besides the matrix.
 template <class S> struct IterArgs {
@@ -337,7 +347,18 @@ template <class S> struct IterArgs {
     const uint8_t* deferred; // MODE_PEER: per work unit, 1 = reads halo entries (needs the halo wait first); may be null
     int serpentine;          // odd launches walk the work units backwards (what was touched last is re-read first: L2)
     int unit_start;          // rotation of the unit walk (see walk_units)
+    int halo_base;           // MODE_PEER: first halo index of the vector buffers (peers write there WHILE this kernel
+                             // runs, so those entries are read with coherent loads, see ld_x); INT32_MAX otherwise
 };
+
+// Gather of one x entry.  Own entries were written by the previous launch of this GPU: read-only for this
+// kernel's lifetime, so they take the non-coherent path (ld.global.nc through L1).  Halo entries (index >=
+// halo_base, MODE_PEER only) are stored by peer GPUs while this kernel is already running and are read only
+// after the acquire of the owner's flag: PTX allows ld.global.nc only for data nobody writes during the kernel,
+// so they use ld.global.cg (L2, coherent with the peers' NVLink stores).
+template <class S> __device__ __forceinline__ S ld_x(const S* u, int idx, int halo_base) {
+    return idx < halo_base ? Sc<S>::ldg(u + idx) : Sc<S>::ldcg(u + idx);
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
     unsigned long long v;
@@ -351,6 +372,12 @@ __device__ __forceinline__ double ld_volatile_f64(const double* p) {
     double v;
     asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
     return v;
+}
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 
 // Spins (one thread, acquire loads: measured cheaper than relaxed loads + a system fence) until the flags of
@@ -455,6 +482,7 @@ __device__ void control_cta(const IterArgs<S>& it, bool advance) {
         // are with you"; then wait for q's flag in return.
         const PeerArgs& pa = *it.peer;
         const int q = threadIdx.x;
+        const unsigned long long t_pub = (pa.stats && threadIdx.x == 0) ? global_ns() : 0ull;
         if (q < pa.nranks) {
             int okq = 1;
             const int slot = ((j + kRing) % kRing) * kMaxPeers * 4 + pa.rank * 4;
@@ -477,6 +505,10 @@ __device__ void control_cta(const IterArgs<S>& it, bool advance) {
             s_okv[q] = okq;
         }
         __syncthreads();
+        if (pa.stats && threadIdx.x == 0 && fold) {
+            pa.stats[0] += global_ns() - t_pub;  // control CTAs are ordered by the stream: plain updates
+            pa.stats[1] += 1ull;
+        }
     }
     if (threadIdx.x != 0) return;
     int ok = 1;
@@ -505,6 +537,26 @@ __device__ void control_cta(const IterArgs<S>& it, bool advance) {
 template <class S>
 __global__ void __launch_bounds__(256) control_kernel(IterArgs<S> it) {
     control_cta<S, 256>(it, false);
+}
+
+// Device-side barrier of the ranks of a MODE_PEER group: thread q announces this rank's arrival at gate
+// `epoch` in rank q's gate_in[rank] and spins until rank q has announced the same.  The kernel (and with it
+// everything queued behind it on the stream) completes within a couple of microseconds of the LAST rank's
+// arrival, on every rank.  Used where the host would otherwise need a collective: before the first launch of a
+// solve (no rank may store into a peer's ring buffers before that peer has reset them) and in front of a timed
+// batch of trips, so that the ranks' event timers start together whatever the skew of the host threads.
+__global__ void __launch_bounds__(32) peer_gate_kernel(const PeerArgs* pa_ptr, unsigned long long epoch, PowerState* st) {
+    const PeerArgs& pa = *pa_ptr;
+    const int q = threadIdx.x;
+    if (q >= pa.nranks || q == pa.rank) return;
+    st_release_sys(pa.peer_gate[q], epoch);
+    if (pa.debug_nowait) return;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(pa.gate_in + q) < epoch)
+        if (clock64() - t0 > pa.spin_limit) {
+            *(volatile int*)&st->error = 1;
+            return;
+        }
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -539,7 +591,24 @@ template <class S> __device__ __forceinline__ S* ring_buf(const IterArgs<S>& it,
 template <class S>
 __device__ __forceinline__ void halo_wait_warp(const IterArgs<S>& it, const LaunchCtx& c) {
     if ((threadIdx.x & 31) == 0) {
-        if (!wait_peer_flags(*it.peer, it.peer->halo_src_mask, c.flagv)) *(volatile int*)&it.st->error = 1;
+        const PeerArgs& pa = *it.peer;
+        if (pa.stats) {
+            // instrumented form: was the flag already there, and if not, how long did this warp spin
+            bool there = true;
+            for (int q = 0; q < pa.nranks; ++q)
+                if (q != pa.rank && ((pa.halo_src_mask >> q) & 1u) && ld_acquire_sys(pa.flag_in + q) < c.flagv) there = false;
+            atomicAdd(pa.stats + 5, 1ull);
+            if (!there) {
+                const unsigned long long t0 = global_ns();
+                if (!wait_peer_flags(pa, pa.halo_src_mask, c.flagv)) *(volatile int*)&it.st->error = 1;
+                const unsigned long long dt = global_ns() - t0;
+                atomicAdd(pa.stats + 2, dt);
+                atomicAdd(pa.stats + 3, 1ull);
+                atomicMax(pa.stats + 4, dt);
+            }
+        } else if (!wait_peer_flags(pa, pa.halo_src_mask, c.flagv)) {
+            *(volatile int*)&it.st->error = 1;
+        }
     }
     __syncwarp();
 }
@@ -639,8 +708,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    const S* u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     const int nunits = (A.rows + BLOCK - 1) / BLOCK;
     walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nunits, [&](int unit) {
@@ -648,7 +718,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
         if (row < A.rows) {
             const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
             S acc = Sc<S>::zero();
-            for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), Sc<S>::ldg(u + __ldg(A.colidx + p)));
+            for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), ld_x<S>(u, __ldg(A.colidx + p), hb));
             row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, are, aim, qn);
         }
     });
@@ -671,8 +741,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    const S* u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     constexpr int RPU = BLOCK / LANES;  // rows per unit
     const int sub = threadIdx.x % LANES;
@@ -683,7 +754,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
         if (row < A.rows) {
             const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
             for (int p = p0 + sub; p < p1; p += LANES)
-                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), Sc<S>::ldg(u + ld_stream_s32(A.colidx + p)));
+                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), ld_x<S>(u, ld_stream_s32(A.colidx + p), hb));
         }
 #pragma unroll
         for (int d = LANES / 2; d > 0; d >>= 1) Sc<S>::add(acc, Sc<S>::shfl_down(acc, d, LANES));
@@ -722,8 +793,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    const S* u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     const double* vals_d = reinterpret_cast<const double*>(A.vals);
     walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nblk, [&](int b) {
@@ -737,7 +809,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
             // one long row: CTA-strided partial sums, then a CTA reduction (real and imaginary parts).
             S acc = Sc<S>::zero();
             for (int p = p0 + threadIdx.x; p < p1; p += BLOCK)
-                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), Sc<S>::ldg(u + ld_stream_s32(A.colidx + p)));
+                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), ld_x<S>(u, ld_stream_s32(A.colidx + p), hb));
             double ar, ai = 0.0, dummy = 0.0;
             if constexpr (Sc<S>::is_complex) {
                 ar = acc.x;
@@ -764,8 +836,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                     v0 = vv.x;
                     v1 = vv.y;
                 }
-                prod[e - base] = Sc<S>::mul(v0, Sc<S>::ldg(u + cc.x));
-                prod[e - base + 1] = Sc<S>::mul(v1, Sc<S>::ldg(u + cc.y));
+                prod[e - base] = Sc<S>::mul(v0, ld_x<S>(u, cc.x, hb));
+                prod[e - base + 1] = Sc<S>::mul(v1, ld_x<S>(u, cc.y, hb));
             }
             __syncthreads();
             for (int i = threadIdx.x; i < nr; i += BLOCK) {
@@ -832,8 +904,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, co
     if (threadIdx.x == 0) mbar_init(&bar, 1);
     load_sends<S>(it, c, sends);  // ends with a CTA barrier: the mbarrier is initialised for everyone
     S* xs = reinterpret_cast<S*>(window_smem);
-    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    const S* u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     unsigned parity = 0;
     const int nunits = (A.rows + BLOCK - 1) / BLOCK;
@@ -855,7 +928,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, co
             for (int p = p0; p < p1; ++p) {
                 const int col = __ldg(A.colidx + p);
                 const unsigned k = unsigned(col - w.x);
-                const S x = k < unsigned(w.y) ? xs[k] : Sc<S>::ldg(u + col);
+                const S x = k < unsigned(w.y) ? xs[k] : ld_x<S>(u, col, hb);
                 Sc<S>::mac(acc, __ldg(A.vals + p), x);
             }
             const unsigned kd = unsigned(row - w.x);
@@ -885,8 +958,9 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    const S* u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     const int lane = threadIdx.x & 31;
     const int gwarp = ((blockIdx.x - 1) * BLOCK + threadIdx.x) >> 5;
@@ -921,7 +995,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
             }
 #pragma unroll
             for (int r = 0; r < R; ++r)
-                if (col[r] >= 0) Sc<S>::mac(acc[r], v[r], Sc<S>::ldg(u + col[r]));
+                if (col[r] >= 0) Sc<S>::mac(acc[r], v[r], ld_x<S>(u, col[r], hb));
             vp += 32 * R;
             cp += 32 * R;
         }
@@ -958,8 +1032,9 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
     if (it.mode == MODE_PEER) halo_wait_cta<S>(it, c);  // every row reads the whole halo
-    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    const S* u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int hb = it.halo_base;
     const int cta = blockIdx.x - 1;
     const int tile = cta / A.nseg, seg = cta % A.nseg;
     const int c0 = int(int64_t(A.cols) * seg / A.nseg), c1 = int(int64_t(A.cols) * (seg + 1) / A.nseg);
@@ -971,7 +1046,7 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     for (int cb = c0; cb < c1; cb += kGemvChunk) {
         const int nc = min(kGemvChunk, c1 - cb);
         __syncthreads();
-        for (int j = threadIdx.x; j < nc; j += BLOCK) xs[j] = Sc<S>::scale(Sc<S>::ldg(u + cb + j), c.s);
+        for (int j = threadIdx.x; j < nc; j += BLOCK) xs[j] = Sc<S>::scale(ld_x<S>(u, cb + j, hb), c.s);
         __syncthreads();
         if (live) {
             const S* col = A.a + int64_t(cb) * A.lda + r;

@@ -12,12 +12,19 @@
 //
 // One addition that is invisible to callers: because a Matrix can never move, it can carry a handle
 // to its device-resident copy.  The slot is opaque here (power_method.hpp owns its
-// meaning) and is dropped whenever mutable access to the stored matrix is handed out.
+// meaning).  The non-const cast<T>() returns a long-lived T& (the reference's own tests keep one:
+// test/matrix_wrapper_test.cpp:44,82), through which the host matrix can change at any later time without
+// this class noticing -- so the first mutable cast drops the device copy AND switches caching off for this
+// Matrix for good: from then on every solve uploads what the host holds at that moment, exactly what the
+// reference would compute on.  A Matrix only ever read through the const interface (what powerMethod
+// itself uses) uploads once.  The slot is guarded by a mutex: concurrent powerMethod calls on one const
+// Matrix take turns instead of racing on it.
 #include <Eigen/Dense>
 #include <Eigen/Sparse>
 
 #include <cstddef>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <typeinfo>
 #include <vector>
@@ -67,7 +74,12 @@ public:
     template <typename T>
     T& cast() {
         require<T>();
-        device_slot_.reset();  // the caller may now modify the matrix: any device copy is stale
+        {
+            // the caller may modify the matrix through this reference now or at any later time
+            std::lock_guard<std::mutex> lock(device_mutex_);
+            device_slot_.reset();
+            device_cacheable_ = false;
+        }
         return static_cast<BoxTyped<T>*>(box_.get())->get();
     }
     template <typename T>
@@ -76,8 +88,10 @@ public:
         return static_cast<const BoxTyped<T>*>(box_.get())->get();
     }
 
-    // Opaque slot for the device-resident copy (used by power_method.hpp only).
+    // Device-resident copy (used by power_method.hpp only; hold device_mutex() around both).
     std::shared_ptr<void>& device_slot() const { return device_slot_; }
+    bool device_cacheable() const { return device_cacheable_; }
+    std::mutex& device_mutex() const { return device_mutex_; }
 
 private:
     template <typename T>
@@ -103,6 +117,8 @@ private:
     const std::type_info* scalar_;
     std::unique_ptr<Box> box_;
     mutable std::shared_ptr<void> device_slot_;
+    mutable std::mutex device_mutex_;
+    bool device_cacheable_ = true;
 };
 
 }  // namespace EigSol

@@ -14,17 +14,22 @@
 //   * x0 = Vector<Scalar>::Random(n); x0.normalize();     (:62) -- the same Eigen expression, hence the
 //     same std::rand() stream and bit-identical start vector;
 //   * powerMethod: "powerMethod: scalar type mismatch"    (:137-139), then the dense/sparse dispatch.
-// Device scalars are double and std::complex<double>; other ScalarConcept types have no device type and
-// throw "powerMethod: scalar type not supported on the B200 path" (after the shape checks).
+// Device scalars are double and std::complex<double>.  float / std::complex<float> inputs (ScalarConcept admits
+// them, reference src/core/types.hpp:28-30) draw x0 in their own precision exactly as the reference does (same
+// rand() stream), are promoted to double on the host, run the same device loop and are cast back -- the result
+// is at least as accurate as the reference's float loop, iteration counts can differ by rounding.  long double has
+// no device type: "powerMethod: scalar type not supported on the B200 path" (after the shape checks).
 //
 // powerMethod(M, ...) keeps M's device-resident copy alive in M (a Matrix cannot move), so repeated
-// solves on the same Matrix upload and transpose only once.
+// solves on the same Matrix upload and transpose only once -- unless a mutable reference to the stored matrix
+// was ever handed out (matrix.hpp), in which case every solve uploads afresh.
 #include <Eigen/Dense>
 #include <Eigen/Sparse>
 
 #include <cmath>
 #include <complex>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
@@ -45,6 +50,20 @@ template <>
 inline constexpr int dtype_code<double> = EIGSOL_B200_F64;
 template <>
 inline constexpr int dtype_code<std::complex<double>> = EIGSOL_B200_C128;
+
+// the double-precision scalar a single-precision input is promoted to (void: no device path)
+template <typename S>
+struct promoted {
+    using type = void;
+};
+template <>
+struct promoted<float> {
+    using type = double;
+};
+template <>
+struct promoted<std::complex<float>> {
+    using type = std::complex<double>;
+};
 
 template <typename Mat>
 inline constexpr bool is_sparse_v = std::is_base_of_v<Eigen::SparseMatrixBase<Mat>, Mat>;
@@ -96,7 +115,32 @@ EigenResult<typename Mat::Scalar> solve(const Mat& A, const SolverOptions& opts,
     const auto n = A.rows();
     if (n != A.cols()) throw std::runtime_error("powerMethod: matrix must be square");
     if (n == 0) throw std::runtime_error("powerMethod: matrix has zero size");
-    if constexpr (dtype_code<Scalar> < 0) {
+    if constexpr (dtype_code<Scalar> < 0 && !std::is_void_v<typename promoted<Scalar>::type>) {
+        // single precision: x0 exactly as the reference draws it, then everything in double on the device
+        using Wide = typename promoted<Scalar>::type;
+        Vector<Scalar> x0s = Vector<Scalar>::Random(n);
+        x0s.normalize();
+        Vector<Wide> x0 = x0s.template cast<Wide>();
+        x0.normalize();
+        if (!slot) {
+            if constexpr (is_sparse_v<Mat>) {
+                const Eigen::SparseMatrix<Wide, Eigen::ColMajor, int> wide = A.template cast<Wide>();
+                slot = upload(wide);
+            } else {
+                const Eigen::Matrix<Wide, Eigen::Dynamic, Eigen::Dynamic> wide = A.template cast<Wide>();
+                slot = upload(wide);
+            }
+        }
+        Vector<Wide> x(n);
+        double lambda[2] = {0.0, 0.0};
+        int iterations = 0, converged = 0;
+        check(eigsol_b200_power_run(static_cast<eigsol_b200_matrix*>(slot.get()), x0.data(), opts.maxIterations,
+                                    opts.tolerance, x.data(), lambda, &iterations, &converged));
+        Scalar value;
+        if constexpr (std::is_same_v<Scalar, float>) value = static_cast<float>(lambda[0]);
+        else value = Scalar(static_cast<float>(lambda[0]), static_cast<float>(lambda[1]));
+        return EigenResult<Scalar>(value, x.template cast<Scalar>(), iterations, converged != 0);
+    } else if constexpr (dtype_code<Scalar> < 0) {
         throw std::runtime_error("powerMethod: scalar type not supported on the B200 path");
     } else {
         Vector<Scalar> x0 = Vector<Scalar>::Random(n);
@@ -126,8 +170,11 @@ EigenResult<typename Mat::Scalar> powerMethodImpl(const Mat& A, const SolverOpti
 template <ScalarConcept Scalar>
 EigenResult<Scalar> powerMethod(const Matrix& M, const SolverOptions& opts = SolverOptions{}) {
     if (M.scalar_type() != typeid(Scalar)) throw std::runtime_error("powerMethod: scalar type mismatch");
-    if (M.isDense()) return b200_detail::solve(M.cast<Matrix::Dense<Scalar>>(), opts, M.device_slot());
-    return b200_detail::solve(M.cast<Matrix::Sparse<Scalar>>(), opts, M.device_slot());
+    std::lock_guard<std::mutex> lock(M.device_mutex());
+    std::shared_ptr<void> one_shot;  // used instead of M's slot once mutable access to M was handed out
+    std::shared_ptr<void>& slot = M.device_cacheable() ? M.device_slot() : one_shot;
+    if (M.isDense()) return b200_detail::solve(M.cast<Matrix::Dense<Scalar>>(), opts, slot);
+    return b200_detail::solve(M.cast<Matrix::Sparse<Scalar>>(), opts, slot);
 }
 
 }  // namespace EigSol

@@ -12,11 +12,17 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "build", "dropin", "bin")
 
 
-def run(name, timeout=300):
+def run(name, timeout=300, env=None):
     exe = os.path.join(BIN, name)
     if not os.path.exists(exe):
         pytest.skip(f"{exe} not built (needs /root/reference at build time)")
-    return subprocess.run([exe], cwd=BIN, capture_output=True, text=True, timeout=timeout)
+    return subprocess.run([exe], cwd=BIN, capture_output=True, text=True, timeout=timeout,
+                          env=dict(os.environ, **env) if env else None)
+
+
+def gpu_count():
+    import pcsc_eigenvalue_solver_project_b200 as es
+    return es.device_count()
 
 
 @pytest.mark.parametrize("name,count", [("matrix_wrapper_test", 5), ("solve_shifted_test", 8), ("qr_algorithms_test", 10)])
@@ -53,3 +59,37 @@ def test_reference_main_config1():
     vals = [complex(float(a), float(b)) for a, b in nums]
     assert any(abs(v - (5 - 1j)) < 1e-6 for v in vals), r.stdout
     assert any(abs(v - (4 + 5j)) < 1e-6 for v in vals), r.stdout
+
+
+# ---- the same unmodified binaries with the solve sharded over several GPUs inside the one process ----
+@pytest.mark.gpu
+@pytest.mark.parametrize("ngpu", [2, 8])
+def test_reference_power_method_tests_on_a_gpu_group(ngpu):
+    if gpu_count() < ngpu:
+        pytest.skip(f"needs {ngpu} GPUs")
+    env = {"EIGSOL_B200_NGPU": str(ngpu), "EIGSOL_B200_MIN_ROWS_PER_GPU": "1", "EIGSOL_B200_PEER_TIMEOUT_MS": "2000"}
+    r = run("power_method_test", env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "[  PASSED  ] 5 tests." in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ngpu", [2, 8])
+def test_reference_main_config1_on_a_gpu_group(ngpu):
+    if gpu_count() < ngpu:
+        pytest.skip(f"needs {ngpu} GPUs")
+    env = {"EIGSOL_B200_NGPU": str(ngpu), "EIGSOL_B200_MIN_ROWS_PER_GPU": "1", "EIGSOL_B200_PEER_TIMEOUT_MS": "2000"}
+    r = run("main", env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    nums = re.findall(r"\(([-+0-9.e]+),([-+0-9.e]+)\)", r.stdout)
+    vals = [complex(float(a), float(b)) for a, b in nums]
+    assert any(abs(v - (5 - 1j)) < 1e-6 for v in vals), r.stdout
+    assert any(abs(v - (4 + 5j)) < 1e-6 for v in vals), r.stdout
+
+
+# ---- device-resident Matrix cache: one upload per Matrix, never a stale device copy ----
+@pytest.mark.gpu
+def test_matrix_device_cache_reuse_and_invalidation():
+    r = run("device_cache_test")
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "[  PASSED  ] 5 tests." in r.stdout

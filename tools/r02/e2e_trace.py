@@ -1,0 +1,23 @@
+"""Phase trace (EIGSOL_B200_TRACE=1) of the one-shot reference-facing call on C5 at the driver's 20 trips: where the
+e2e time goes.  Run twice so the second call sees warm pinned pools / contexts."""
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import pcsc_eigenvalue_solver_project_b200 as es
+from pcsc_eigenvalue_solver_project_b200 import generators as gen
+
+g = int(os.environ.get("GRID", 256))
+n = g ** 3
+rp, ci, v = gen.laplacian_3d(g)
+outer, inner, vals = gen.csr_to_csc_hermitian(rp, ci, v)
+M = es.Matrix(((n, n), outer, inner, vals))
+x0 = es.random_unit(n, np.float64, seed=1)
+for rep in range(3):
+    t0 = time.perf_counter()
+    r = es.powerMethod(M, es.SolverOptions(20, -1.0), x0=x0)
+    dt = time.perf_counter() - t0
+    print(f"== call {rep}: {dt * 1e3:.1f} ms, {20 / dt:.1f} it/s, lambda {r.eigenvalue!r}", file=sys.stderr, flush=True)
