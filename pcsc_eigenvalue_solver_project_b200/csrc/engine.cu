@@ -30,6 +30,7 @@
 namespace eigsol_b200 {
 
 static thread_local std::string g_last_error;
+static thread_local const void* g_preload_x0 = nullptr;  // set by the one-shot CSC call around its matrix creation
 static std::atomic<int64_t> g_matrices_created{0};  // device uploads of whole matrices so far (tests of the Matrix cache)
 
 // -------------------------------------------------------------------------------------------------
@@ -100,11 +101,17 @@ struct Trace {
     bool on;
     std::chrono::steady_clock::time_point t0;
     Trace() : on(std::getenv("EIGSOL_B200_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    void mark_async(const char* what) {  // host-side mark: does not wait for the device
+        if (!on) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[eigsol_b200] %-36s %8.2f ms (host)\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
     void mark(const char* what) {
         if (!on) return;
         cudaDeviceSynchronize();
         const auto t1 = std::chrono::steady_clock::now();
-        std::fprintf(stderr, "[eigsol_b200] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        std::fprintf(stderr, "[eigsol_b200] %-36s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
         t0 = t1;
     }
 };
@@ -261,6 +268,8 @@ struct MatrixImpl {
     unsigned long long flag_epoch = 0;  // MODE_PEER: flag base of the current solve (identical on every rank)
     bool begun = false;
     int max_trips = 0;
+    const void* preload_x0 = nullptr;  // one-shot call: host start vector to upload together with the matrix
+    bool x0_preloaded = false;         // ... and it is in buf[0] already (consumed by the next begin() with that pointer)
     cudaGraphExec_t graph = nullptr, graph_short = nullptr;  // graph_len launches / kRing launches
     int graph_len = 0;
 
@@ -350,9 +359,10 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
 void MatrixImpl::alloc_vectors() {
     nloc_pad = (nloc + 15) / 16 * 16;
     ext_len = nloc_pad + nhalo;
-    for (auto& b : buf) b.alloc(size_t(ext_len) * ss(), 256);
+    for (auto& b : buf)
+        if (!(b.p && b.bytes == size_t(ext_len) * ss())) b.alloc(size_t(ext_len) * ss(), 256);  // buf[0] may be in place already (preloaded x0)
     d_xloc.alloc(size_t(std::max<int64_t>(nloc, 1)) * ss());
-    d_xglob.alloc(size_t(std::max<int64_t>(n, 1)) * ss());
+    if (nranks > 1 && !(comm && comm->local)) d_xglob.alloc(size_t(std::max<int64_t>(n, 1)) * ss());  // NCCL gather target
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -628,13 +638,14 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
 // -------------------------------------------------------------------------------------------------
 void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
                                         const void* values) {
+    Trace tr;
     dense = false;
     if (rows > INT32_MAX || cols > INT32_MAX) throw PlanError("matrix dimension exceeds int32 indices");
     if (!outer) throw PlanError("null outer index array");
     if (outer[0] != 0) throw PlanError("CSC outer index must start at 0 (compressed storage expected)");
-    for (int64_t j = 0; j < cols; ++j)
-        if (outer[j + 1] < outer[j]) throw PlanError("CSC outer index not monotone");
+    // outer[cols] sizes the allocations; the monotonicity of outer and the range of inner are checked on the device
     const int64_t nnz = outer[cols];
+    if (nnz < 0) throw PlanError("CSC outer index not monotone");
     if (nnz > 0 && (!inner || !values)) throw PlanError("null inner index array");
     row_begin.assign({0, rows});
     lo = 0;
@@ -644,64 +655,68 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
     halo.peer_count.assign(1, 0);
     halo.peer_off.assign(2, 0);
     nhalo = 0;
-    alloc_vectors();
-    if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
-    plan_exchange();
-    setup_peer();
-    csr = CsrHost();
-    csr.dtype = dtype;
-    csr.rows = rows;
-    csr.cols = ext_len;
-    Trace tr;
-    tr.mark("ingest: validate+vectors");
     const size_t s = size_t(ss());
     const size_t nz = size_t(std::max<int64_t>(nnz, 1));
-    d_rowptr.alloc(sizeof(int32_t) * size_t(rows + 1));  // zero-filled: the row histogram
-    d_colidx.alloc(sizeof(int32_t) * nz);
-    d_vals.alloc(nz * s);
     stats = RowStats();
     stats.rows = rows;
     stats.nnz = nnz;
+    csr = CsrHost();
+    csr.dtype = dtype;
+    csr.rows = rows;
     if (nnz > 0) {
+        // The PCIe copy of the three arrays is what bounds this call, so it starts first and everything else hides
+        // behind it: the uploader threads push outer, inner, values (in that order) while this thread allocates the
+        // rest; as soon as outer + inner have landed the expansion, the sort by row and the row-pointer scan run on
+        // the device UNDER the values upload; only the final gather waits for the values.
         DevBuf d_outer, d_inner, d_cvals, d_col, d_iota, d_perm, d_keys, d_flags, d_tmp, d_tmp2;
-        d_outer.alloc(sizeof(int32_t) * size_t(cols + 1));
-        d_inner.alloc(sizeof(int32_t) * nz);
-        d_cvals.alloc(nz * s);
-        d_col.alloc(sizeof(int32_t) * nz);
-        d_iota.alloc(sizeof(int32_t) * nz);
-        d_perm.alloc(sizeof(int32_t) * nz);
-        d_keys.alloc(sizeof(int32_t) * nz);
-        d_flags.alloc(64);
-        tr.mark("ingest: device allocs");
+        d_outer.alloc_raw(sizeof(int32_t) * size_t(cols + 1));
+        d_inner.alloc_raw(sizeof(int32_t) * nz);
+        d_cvals.alloc_raw(nz * s);
         StagedUploader up;
         up.add(d_outer.p, outer, sizeof(int32_t) * size_t(cols + 1));
-        up.add(d_inner.p, inner, sizeof(int32_t) * size_t(nnz));
+        const size_t index_jobs = up.add(d_inner.p, inner, sizeof(int32_t) * size_t(nnz));
         up.add(d_cvals.p, values, size_t(nnz) * s);
-        EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
-        tr.mark("ingest: staged upload");
-        const int B = 256;
-        const unsigned gnz = unsigned((nnz + B - 1) / B);
-        csc_expand_kernel<<<gnz, B, 0, stream>>>(d_outer.as<int32_t>(), d_inner.as<int32_t>(), cols, rows, nnz,
-                                                  d_col.as<int32_t>(), d_iota.as<int32_t>(), d_rowptr.as<int32_t>(),
-                                                  d_flags.as<int>());
+        if (preload_x0) {
+            // one-shot call: the start vector rides on the same upload (begin() then finds it in place)
+            buf[0].alloc(size_t((rows + 15) / 16 * 16) * s, 256);
+            up.add(buf[0].p, preload_x0, size_t(rows) * s);
+        }
+        up.start(device, upload_threads(nranks), index_jobs);
+        tr.mark_async("ingest: allocs + upload started");
+        alloc_vectors();
+        if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
+        plan_exchange();
+        setup_peer();
+        csr.cols = ext_len;
+        d_rowptr.alloc(sizeof(int32_t) * size_t(rows + 1));  // zero-filled: the row histogram
+        d_colidx.alloc_raw(sizeof(int32_t) * nz);
+        d_vals.alloc_raw(nz * s);
+        d_col.alloc_raw(sizeof(int32_t) * nz);
+        d_iota.alloc_raw(sizeof(int32_t) * nz);
+        d_perm.alloc_raw(sizeof(int32_t) * nz);
+        d_keys.alloc_raw(sizeof(int32_t) * nz);
+        d_flags.alloc(64);
         int end_bit = 1;
         while (end_bit < 31 && (int64_t(1) << end_bit) < rows) ++end_bit;
         size_t tb = 0, tb2 = 0;
         EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_inner.as<int32_t>(), d_keys.as<int32_t>(),
                                                     d_iota.as<int32_t>(), d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
-        d_tmp.alloc(tb);
+        d_tmp.alloc_raw(tb);
+        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(rows + 1), stream));
+        d_tmp2.alloc_raw(tb2);
+        tr.mark_async("ingest: remaining allocs");
+        up.wait_prefix();
+        tr.mark_async("ingest: outer + inner on the device");
+        const int B = 256;
+        const unsigned gnz = unsigned((nnz + B - 1) / B);
+        outer_check_kernel<<<unsigned((cols + B - 1) / B), B, 0, stream>>>(d_outer.as<int32_t>(), cols, nnz, d_flags.as<int>());
+        csc_expand_kernel<<<gnz, B, 0, stream>>>(d_outer.as<int32_t>(), d_inner.as<int32_t>(), cols, rows, nnz,
+                                                  d_col.as<int32_t>(), d_iota.as<int32_t>(), d_rowptr.as<int32_t>(),
+                                                  d_flags.as<int>());
         EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(d_tmp.p, tb, d_inner.as<int32_t>(), d_keys.as<int32_t>(),
                                                     d_iota.as<int32_t>(), d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
-        EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(rows + 1), stream));
-        d_tmp2.alloc(tb2);
         EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp2.p, tb2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(rows + 1), stream));
-        if (dtype)
-            csc_gather_kernel<double2><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_cvals.as<double2>(), nnz,
-                                                              d_colidx.as<int32_t>(), d_vals.as<double2>());
-        else
-            csc_gather_kernel<double><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_cvals.as<double>(), nnz,
-                                                             d_colidx.as<int32_t>(), d_vals.as<double>());
-        // row-length statistics for the kernel choice
+        // row-length statistics for the kernel choice (needs only rowptr)
         int* f = d_flags.as<int>();  // [0] error flags, [1] max, [2] min, [4..5] padded (u64), [6..7] var (double)
         const int init_min = INT32_MAX;
         EIGSOL_CUDA(cudaMemcpyAsync(f + 2, &init_min, sizeof(int), cudaMemcpyHostToDevice, stream));
@@ -709,14 +724,24 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         const unsigned gsl = unsigned(((rows + 63) / 64 + B - 1) / B);
         row_stats_kernel<<<gsl, B, 0, stream>>>(d_rowptr.as<int32_t>(), rows, stats.mean, f + 1, f + 2,
                                                 reinterpret_cast<unsigned long long*>(f + 4), reinterpret_cast<double*>(f + 6));
-        launches += 4;
+        EIGSOL_CUDA(cudaGetLastError());
+        EIGSOL_CUDA(up.finish());
+        x0_preloaded = preload_x0 != nullptr;
+        tr.mark_async("ingest: values on the device");
+        if (dtype)
+            csc_gather_kernel<double2><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_cvals.as<double2>(), nnz,
+                                                              d_colidx.as<int32_t>(), d_vals.as<double2>());
+        else
+            csc_gather_kernel<double><<<gnz, B, 0, stream>>>(d_perm.as<int32_t>(), d_col.as<int32_t>(), d_cvals.as<double>(), nnz,
+                                                             d_colidx.as<int32_t>(), d_vals.as<double>());
+        launches += 6;
         EIGSOL_CUDA(cudaGetLastError());
         int hf[8];
         EIGSOL_CUDA(cudaMemcpyAsync(hf, f, sizeof hf, cudaMemcpyDeviceToHost, stream));
         EIGSOL_CUDA(cudaStreamSynchronize(stream));
-        tr.mark("ingest: transpose+stats");
-        if (hf[0] & 2) throw PlanError("CSC inner index out of range");
+        tr.mark("ingest: gather + stats");
         if (hf[0] & 1) throw PlanError("CSC outer index not monotone");
+        if (hf[0] & 2) throw PlanError("CSC inner index out of range");
         unsigned long long padded;
         double var;
         std::memcpy(&padded, hf + 4, sizeof padded);
@@ -725,11 +750,20 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         stats.min = hf[2];
         stats.cv = stats.mean > 0 ? std::sqrt(var / double(rows)) / stats.mean : 0.0;
         stats.sell_fill = double(padded) / double(nnz);
+    } else {
+        alloc_vectors();
+        plan_exchange();
+        setup_peer();
+        csr.cols = ext_len;
+        d_rowptr.alloc(sizeof(int32_t) * size_t(rows + 1));
+        d_colidx.alloc(sizeof(int32_t) * nz);
+        d_vals.alloc(nz * s);
     }
     const int forced = env_int("EIGSOL_B200_KERNEL", 0);
     if ((forced > 0 && forced <= K_SELL) || forced == K_CSR_WINDOW) set_kernel(forced, env_int("EIGSOL_B200_LANES", 0));
     else set_kernel(K_AUTO, 0);
     compute_prescale();
+    tr.mark("ingest: kernel choice + prescale");
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -1451,10 +1485,22 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol, bool unit_scale) 
     issued = 0;
     const size_t s = size_t(ss());
     EIGSOL_CUDA(cudaMemcpyAsync(d_state.p, &st, sizeof st, cudaMemcpyHostToDevice, stream));
-    for (auto& b : buf) EIGSOL_CUDA(cudaMemsetAsync(b.p, 0, size_t(ext_len) * s, stream));
-    if (nloc)
-        EIGSOL_CUDA(cudaMemcpyAsync(buf[0].p, static_cast<const char*>(x0) + size_t(lo) * s, size_t(nloc) * s,
-                                    cudaMemcpyHostToDevice, stream));
+    const bool in_place = x0_preloaded && x0 == preload_x0;  // one-shot call: x0 came up with the matrix
+    x0_preloaded = false;
+    preload_x0 = nullptr;
+    for (int b = in_place ? 1 : 0; b < kRing; ++b) EIGSOL_CUDA(cudaMemsetAsync(buf[b].p, 0, size_t(ext_len) * s, stream));
+    if (nloc && !in_place) {
+        const char* src = static_cast<const char*>(x0) + size_t(lo) * s;
+        if (size_t(nloc) * s >= (size_t(32) << 20)) {
+            // a large pageable vector: several host threads through pinned staging instead of one synchronous copy
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));  // the zero fill above must not land after the upload
+            StagedUploader up;
+            up.add(buf[0].p, src, size_t(nloc) * s);
+            EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+        } else {
+            EIGSOL_CUDA(cudaMemcpyAsync(buf[0].p, src, size_t(nloc) * s, cudaMemcpyHostToDevice, stream));
+        }
+    }
     if (dense) EIGSOL_CUDA(cudaMemsetAsync(d_tile_ticket.p, 0, sizeof(unsigned) * size_t(ntiles), stream));
     if (nranks > 1) {
         // x0 is global on every rank: the halo of launch 0 comes straight from it (no exchange needed).  The halo
@@ -1647,17 +1693,25 @@ void MatrixImpl::step(int trips, float* ms_out) {
 // Local slice on the device -> global vector on the host (every rank gets the full vector).
 void MatrixImpl::gather_download(const void* d_local, void* host_out) {
     const size_t s = size_t(ss());
+    auto download = [&](void* dst, const void* src, size_t bytes) {
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));  // src is complete
+        if (bytes >= (size_t(32) << 20)) {
+            StagedUploader down;  // device -> pinned -> pageable host array, several threads
+            down.download = true;
+            down.add(dst, src, bytes);
+            EIGSOL_CUDA(down.run(device, upload_threads(nranks)));
+        } else if (bytes) {
+            EIGSOL_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream));
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        }
+    };
     if (nranks == 1) {
-        if (n) EIGSOL_CUDA(cudaMemcpyAsync(host_out, d_local, size_t(n) * s, cudaMemcpyDeviceToHost, stream));
-        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        download(host_out, d_local, size_t(n) * s);
         return;
     }
     if (comm->local) {
         // single process: host_out is the SAME buffer on every rank; each writes its own rows
-        if (nloc)
-            EIGSOL_CUDA(cudaMemcpyAsync(static_cast<char*>(host_out) + size_t(lo) * s, d_local, size_t(nloc) * s,
-                                        cudaMemcpyDeviceToHost, stream));
-        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        download(static_cast<char*>(host_out) + size_t(lo) * s, d_local, size_t(nloc) * s);
         comm->local->barrier();  // the whole vector is in place when any rank returns
         return;
     }
@@ -2030,6 +2084,7 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
         m.init_common(dtype, comm ? &comm->impl : nullptr);
         m.n = rows;
         if (m.nranks == 1 && env_int("EIGSOL_B200_DEVICE_INGEST", 1)) {
+            m.preload_x0 = g_preload_x0;
             m.init_sparse_device_csc(rows, cols, outer, inner, values);
             *out = h.release();
             ++g_matrices_created;
@@ -2357,7 +2412,9 @@ int eigsol_b200_power_csc(int dtype, int64_t rows, int64_t cols, const int32_t* 
                           const void* values, const void* x0, int max_iterations, double tolerance, void* x_out,
                           double lambda_out[2], int* iterations_out, int* converged_out) {
     eigsol_b200_matrix* m = nullptr;
+    g_preload_x0 = x0;  // the start vector goes up together with the matrix (single GPU)
     int e = eigsol_b200_matrix_create_csc(dtype, rows, cols, outer, inner, values, nullptr, &m);
+    g_preload_x0 = nullptr;
     if (e) return e;
     e = eigsol_b200_power_run(m, x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
     const std::string keep = g_last_error;

@@ -17,6 +17,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <condition_variable>
 #include <cstring>
 #include <mutex>
 #include <cub/device/device_radix_sort.cuh>
@@ -66,6 +67,11 @@ struct PinnedPool {
     }
 };
 
+// Copies between large PAGEABLE host arrays and the device through pinned staging buffers, several host threads, each
+// with its own stream and two buffers (the memcpy of one chunk overlaps the DMA of the previous one).  Jobs run in the
+// order they were added.  start() returns at once; wait_prefix(k) blocks until the first k jobs have landed (so device
+// work that needs only those can start while the rest is still in flight); finish() joins and returns the first CUDA
+// error seen.  download = true reverses the direction (device -> pinned -> host array).
 struct StagedUploader {
     static constexpr size_t kChunk = PinnedPool::kBytes;
     struct Job {
@@ -74,58 +80,113 @@ struct StagedUploader {
         size_t bytes;
     };
     std::vector<Job> jobs;
-    void add(void* dst, const void* src, size_t bytes) {
+    bool download = false;
+    std::vector<std::thread> pool;
+    std::atomic<size_t> next{0};
+    std::atomic<int> err{int(cudaSuccess)};
+    std::mutex mu;
+    std::condition_variable cv;
+    size_t prefix = 0;         // jobs [0, prefix) are the ones wait_prefix() waits for
+    int past_prefix = 0;       // threads that have completed everything they took from the prefix
+    int nthreads_run = 0;
+
+    ~StagedUploader() {
+        for (auto& t : pool)
+            if (t.joinable()) t.join();
+    }
+    size_t add(void* dst, const void* src, size_t bytes) {
         for (size_t off = 0; off < bytes; off += kChunk)
             jobs.push_back(Job{static_cast<char*>(dst) + off, static_cast<const char*>(src) + off,
                                std::min(kChunk, bytes - off)});
+        return jobs.size();
     }
-    // Runs all jobs; returns the first CUDA error seen (cudaSuccess if none).
-    cudaError_t run(int device, int nthreads) {
-        if (jobs.empty()) return cudaSuccess;
-        nthreads = int(std::max<size_t>(1, std::min<size_t>(size_t(nthreads), jobs.size())));
-        nthreads = std::min(nthreads, 16);
-        std::atomic<size_t> next{0};
-        std::atomic<int> err{int(cudaSuccess)};
-        auto worker = [&](int) {
-            cudaSetDevice(device);
-            void* pin[2] = {nullptr, nullptr};
-            cudaStream_t st = nullptr;
-            cudaEvent_t ev[2] = {nullptr, nullptr};
-            cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
-            for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
-                e = PinnedPool::get().acquire(&pin[b]);
-                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming);
-            }
-            int b = 0;
-            bool used[2] = {false, false};
-            while (e == cudaSuccess) {
-                const size_t i = next.fetch_add(1);
-                if (i >= jobs.size()) break;
-                if (used[b]) e = cudaEventSynchronize(ev[b]);  // the DMA out of this buffer has finished
-                if (e != cudaSuccess) break;
-                std::memcpy(pin[b], jobs[i].src, jobs[i].bytes);
-                e = cudaMemcpyAsync(jobs[i].dst, pin[b], jobs[i].bytes, cudaMemcpyHostToDevice, st);
-                if (e == cudaSuccess) e = cudaEventRecord(ev[b], st);
-                used[b] = true;
-                b ^= 1;
-            }
-            if (st) {
-                const cudaError_t e2 = cudaStreamSynchronize(st);
-                if (e == cudaSuccess) e = e2;
-            }
-            for (int k = 0; k < 2; ++k) {
-                if (ev[k]) cudaEventDestroy(ev[k]);
-                PinnedPool::get().release(pin[k]);
-            }
-            if (st) cudaStreamDestroy(st);
-            if (e != cudaSuccess) err.store(int(e));
+    void worker(int device) {
+        cudaSetDevice(device);
+        void* pin[2] = {nullptr, nullptr};
+        cudaStream_t st = nullptr;
+        cudaEvent_t ev[2] = {nullptr, nullptr};
+        cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+        for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+            e = PinnedPool::get().acquire(&pin[b]);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[b], cudaEventDisableTiming);
+        }
+        int b = 0;
+        bool used[2] = {false, false};
+        const Job* pending[2] = {nullptr, nullptr};  // download: chunk sitting in pin[b] that still has to go to the host array
+        bool passed = false;
+        auto drain = [&](int k) {  // the DMA of buffer k has finished; a download now copies it out
+            if (!used[k]) return cudaSuccess;
+            const cudaError_t r = cudaEventSynchronize(ev[k]);
+            if (r == cudaSuccess && pending[k]) std::memcpy(pending[k]->dst, pin[k], pending[k]->bytes);
+            pending[k] = nullptr;
+            used[k] = false;
+            return r;
         };
-        std::vector<std::thread> pool;
-        for (int t = 1; t < nthreads; ++t) pool.emplace_back(worker, t);
-        worker(0);
+        auto pass_prefix = [&] {
+            if (passed) return;
+            passed = true;
+            std::lock_guard<std::mutex> lk(mu);
+            ++past_prefix;
+            cv.notify_all();
+        };
+        while (e == cudaSuccess) {
+            const size_t i = next.fetch_add(1);
+            if (i >= prefix && !passed) {
+                // everything this thread took from the prefix must have landed before it reports
+                for (int k = 0; k < 2 && e == cudaSuccess; ++k) e = drain(k);
+                pass_prefix();
+            }
+            if (i >= jobs.size() || e != cudaSuccess) break;
+            e = drain(b);
+            if (e != cudaSuccess) break;
+            const Job& j = jobs[i];
+            if (download) {
+                e = cudaMemcpyAsync(pin[b], j.src, j.bytes, cudaMemcpyDeviceToHost, st);
+                pending[b] = &j;
+            } else {
+                std::memcpy(pin[b], j.src, j.bytes);
+                e = cudaMemcpyAsync(j.dst, pin[b], j.bytes, cudaMemcpyHostToDevice, st);
+            }
+            if (e == cudaSuccess) e = cudaEventRecord(ev[b], st);
+            used[b] = true;
+            b ^= 1;
+        }
+        for (int k = 0; k < 2; ++k) {
+            const cudaError_t e2 = drain(k);
+            if (e == cudaSuccess) e = e2;
+        }
+        pass_prefix();
+        if (st) {
+            const cudaError_t e2 = cudaStreamSynchronize(st);
+            if (e == cudaSuccess) e = e2;
+        }
+        for (int k = 0; k < 2; ++k) {
+            if (ev[k]) cudaEventDestroy(ev[k]);
+            PinnedPool::get().release(pin[k]);
+        }
+        if (st) cudaStreamDestroy(st);
+        if (e != cudaSuccess) err.store(int(e));
+    }
+    void start(int device, int nthreads, size_t prefix_jobs = 0) {
+        prefix = std::min(prefix_jobs, jobs.size());
+        nthreads_run = int(std::max<size_t>(1, std::min<size_t>(size_t(std::min(nthreads, 16)), std::max<size_t>(jobs.size(), 1))));
+        for (int t = 0; t < nthreads_run; ++t) pool.emplace_back([this, device] { worker(device); });
+    }
+    void wait_prefix() {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return past_prefix >= nthreads_run; });
+    }
+    cudaError_t finish() {
         for (auto& t : pool) t.join();
+        pool.clear();
         jobs.clear();
         return cudaError_t(err.load());
+    }
+    // Runs all jobs and waits; returns the first CUDA error seen (cudaSuccess if none).
+    cudaError_t run(int device, int nthreads) {
+        if (jobs.empty()) return cudaSuccess;
+        start(device, nthreads);
+        return finish();
     }
 };
 
@@ -148,6 +209,14 @@ __global__ void csc_expand_kernel(const int32_t* __restrict__ outer, const int32
     const int32_t r = inner[p];
     if (r < 0 || r >= rows) atomicOr(flags, 2);
     else atomicAdd(rowcount + r, 1);
+}
+
+// flags bit 0: outer not monotone / out of [0, nnz] (host only checked outer[0] == 0 and read outer[cols])
+__global__ void outer_check_kernel(const int32_t* __restrict__ outer, int64_t cols, int64_t nnz, int* flags) {
+    const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (j >= cols) return;
+    const int32_t a = outer[j], b = outer[j + 1];
+    if (b < a || a < 0 || b > nnz) atomicOr(flags, 1);
 }
 
 template <class S>

@@ -1077,15 +1077,32 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     __syncthreads();
     if (!s_tile_last) return;
     __threadfence();
+    // The tail of the launch: only the ntiles last CTAs are still running, so what matters is latency.  The segment
+    // partials (L2-resident) are fetched eight segments at a time -- 8 * R independent loads in flight per thread --
+    // and added in segment order (deterministic).
     double are = 0.0, aim = 0.0, qn = 0.0;
+    if (live) {
+        S z[R];
 #pragma unroll
-    for (int k = 0; k < R; ++k) {
-        const int row = r + k;
-        if (row < A.rows) {
-            S z = Sc<S>::zero();
-            for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
-            row_epilogue<S>(sends, z, Sc<S>::ldg(u + row), out, row, are, aim, qn);
+        for (int k = 0; k < R; ++k) z[k] = Sc<S>::zero();
+        const S* pp = A.partial + r;
+        for (int s0 = 0; s0 < A.nseg; s0 += 8) {
+            S t[8][R];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const bool in = s0 + i < A.nseg;
+#pragma unroll
+                for (int k = 0; k < R; ++k)
+                    t[i][k] = in ? Sc<S>::ldcg(pp + int64_t(s0 + i) * A.lda + k) : Sc<S>::zero();
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int k = 0; k < R; ++k) Sc<S>::add(z[k], t[i][k]);
         }
+#pragma unroll
+        for (int k = 0; k < R; ++k)
+            if (r + k < A.rows) row_epilogue<S>(sends, z[k], Sc<S>::ldg(u + r + k), out, r + k, are, aim, qn);
     }
     cta_finish<S, BLOCK>(it, c, are, aim, qn, tile);
 }

@@ -65,6 +65,12 @@ struct DevBuf {
         EIGSOL_CUDA(cudaMemset(p, 0, n + pad));
         EIGSOL_CUDA(cudaDeviceSynchronize());
     }
+    // no zero fill, no synchronisation: for buffers every byte of which is written before it is read
+    void alloc_raw(size_t n, size_t pad = 64) {
+        release();
+        bytes = n;
+        EIGSOL_CUDA(cudaMalloc(&p, n + pad));
+    }
     void upload(const void* src, size_t n, cudaStream_t s) {
         if (n) EIGSOL_CUDA(cudaMemcpyAsync(p, src, n, cudaMemcpyHostToDevice, s));
     }
