@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <atomic>
 #include <charconv>
+#include <climits>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -380,17 +381,34 @@ struct MappedMatrix {
         if (std::memcmp(h.magic, "EIGSOLB2", 8) != 0 || h.version != 1 || (h.dtype != 0 && h.dtype != 1) || h.rows <= 0 ||
             h.cols <= 0 || h.nnz < 0)
             throw IoError("Not an EIGSOLB2 matrix file");
-        const size_t s = h.dtype ? 16 : 8;
-        size_t off = sizeof(BinHeader);
+        // The header is untrusted input: bound every count before it sizes an offset, compare offsets with the real
+        // file size (the last array may lack its alignment padding, never its payload), and for sparse files check
+        // that the column pointer array agrees with the header -- the arrays go straight to the upload path, which
+        // sizes its reads from outer[cols].
+        if (h.dense != 0 && h.dense != 1) throw IoError("Not an EIGSOLB2 matrix file");
+        if (h.rows > INT32_MAX || h.cols > INT32_MAX) throw IoError("Truncated/corrupt EIGSOLB2 matrix file");
+        if (h.dense ? (h.nnz != h.rows * h.cols) : (h.nnz > INT32_MAX)) throw IoError("Truncated/corrupt EIGSOLB2 matrix file");
+        const uint64_t s = h.dtype ? 16 : 8;
+        const uint64_t size = file.size;
+        uint64_t off = sizeof(BinHeader);
+        auto take = [&](uint64_t bytes, bool last) {  // consumes one array; returns its offset
+            const uint64_t at = off;
+            if (bytes > size || at > size - bytes) throw IoError("Truncated/corrupt EIGSOLB2 matrix file");
+            off = at + bytes;
+            if (!last) {
+                const uint64_t padded = (off + 63) & ~uint64_t(63);
+                if (padded > size) throw IoError("Truncated/corrupt EIGSOLB2 matrix file");
+                off = padded;
+            }
+            return at;
+        };
         if (!h.dense) {
-            outer = reinterpret_cast<const int32_t*>(file.data + off);
-            off += align64(sizeof(int32_t) * size_t(h.cols + 1));
-            inner = reinterpret_cast<const int32_t*>(file.data + off);
-            off += align64(sizeof(int32_t) * size_t(h.nnz));
+            outer = reinterpret_cast<const int32_t*>(file.data + take(sizeof(int32_t) * (uint64_t(h.cols) + 1), false));
+            inner = reinterpret_cast<const int32_t*>(file.data + take(sizeof(int32_t) * uint64_t(h.nnz), false));
         }
-        values = file.data + off;
-        off += align64(s * size_t(h.nnz));
-        if (off > align64(file.size)) throw IoError("Truncated EIGSOLB2 matrix file");
+        values = file.data + take(s * uint64_t(h.nnz), true);
+        if (!h.dense && (outer[0] != 0 || int64_t(outer[h.cols]) != h.nnz))
+            throw IoError("Truncated/corrupt EIGSOLB2 matrix file");
     }
 };
 

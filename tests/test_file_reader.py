@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 import pcsc_eigenvalue_solver_project_b200 as es
+from pcsc_eigenvalue_solver_project_b200 import generators as gen
 from _oracle import Reference, have_reference
 
 REF_DATA = "/root/reference/data"
@@ -162,6 +163,69 @@ def test_binary_container_round_trip_and_rejects_garbage(tmp_path):
         f.write(b"NOTMAGIC")
     with pytest.raises(RuntimeError, match="Not an EIGSOLB2 matrix file"):
         es.readMatrixBinary(p)
+
+
+def _patch(path, offset, fmt, value):
+    import struct
+    with open(path, "r+b") as f:
+        f.seek(offset)
+        f.write(struct.pack(fmt, value))
+
+
+def test_binary_container_rejects_corrupt_headers_and_truncation(tmp_path):
+    """The EIGSOLB2 header is untrusted: wrapped offsets, a short file, a dense flag outside {0,1} and column pointers
+    that disagree with the header must all come back as the IO error, never as an out-of-bounds read.
+    Header layout: magic[8], version i32, dtype i32, dense i32, pad i32, rows i64, cols i64, nnz i64."""
+    import shutil
+    import scipy.sparse as sp
+    g = 6
+    rp, ci, v = gen.laplacian_2d(g)
+    a = sp.csr_matrix((v, ci, rp), shape=(g * g, g * g)).tocsc()
+    good = str(tmp_path / "good.bin")
+    es.writeMatrixBinary(es.Matrix(a), good)
+    m = es.readMatrixBinary(good)
+    assert not m.isDense() and np.array_equal(m._values, a.data)
+    size = os.path.getsize(good)
+    cases = {
+        "nnz_huge": (40, "<q", 2**62),           # s * nnz wraps in 64-bit arithmetic
+        "nnz_above_int32": (40, "<q", 2**31 + 5),
+        "cols_huge": (32, "<q", 2**40),
+        "rows_above_int32": (24, "<q", 2**31),
+        "dense_flag": (16, "<i", 7),
+        "nnz_disagrees_with_outer": (40, "<q", int(a.nnz) - 1),
+    }
+    for name, (off, fmt, val) in cases.items():
+        p = str(tmp_path / f"{name}.bin")
+        shutil.copy(good, p)
+        _patch(p, off, fmt, val)
+        with pytest.raises(RuntimeError, match="EIGSOLB2"):
+            es.readMatrixBinary(p)
+    # outer[0] != 0
+    p = str(tmp_path / "outer0.bin")
+    shutil.copy(good, p)
+    _patch(p, 64, "<i", 1)
+    with pytest.raises(RuntimeError, match="EIGSOLB2"):
+        es.readMatrixBinary(p)
+    # truncation: 100 bytes short loses payload of the values array; 1 byte short of the payload end too
+    payload_end = 64 + ((4 * (g * g + 1) + 63) // 64) * 64 + ((4 * a.nnz + 63) // 64) * 64 + 8 * a.nnz
+    for cut in (size - 100, payload_end - 1):
+        p = str(tmp_path / f"cut{cut}.bin")
+        with open(good, "rb") as f, open(p, "wb") as o:
+            o.write(f.read(cut))
+        with pytest.raises(RuntimeError, match="EIGSOLB2"):
+            es.readMatrixBinary(p)
+    # the alignment padding behind the LAST array is optional
+    p = str(tmp_path / "nopad.bin")
+    with open(good, "rb") as f, open(p, "wb") as o:
+        o.write(f.read(payload_end))
+    m = es.readMatrixBinary(p)
+    assert np.array_equal(m._values, a.data)
+    # dense file whose nnz is not rows * cols
+    d = str(tmp_path / "dense.bin")
+    es.writeMatrixBinary(es.Matrix(np.arange(12.0).reshape(3, 4)), d)
+    _patch(d, 40, "<q", 11)
+    with pytest.raises(RuntimeError, match="EIGSOLB2"):
+        es.readMatrixBinary(d)
 
 
 # ---- the C++ drop-in header (eigsol/src/reader/file_matrix_reader.hpp) ---------------------------------------
