@@ -247,6 +247,7 @@ struct MatrixImpl {
     int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
     int serpentine = 0;
     bool pdl = true;  // programmatic dependent launch of the matvec kernels
+    int gemv_tail = 0;  // EIGSOL_B200_GEMV_TAIL: combine variant of the dense kernel's last CTA per row tile
 
     // dense layout
     DevBuf d_dense, d_dense_partial, d_tile_ticket;
@@ -275,6 +276,7 @@ struct MatrixImpl {
 
     int ss() const { return dtype ? 16 : 8; }
     ~MatrixImpl() {
+        if (stream) cudaStreamSynchronize(stream);  // pooled buffers are handed back after their last use
         for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
         if (graph) cudaGraphExecDestroy(graph);
         if (graph_short) cudaGraphExecDestroy(graph_short);
@@ -346,6 +348,16 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     cudaDeviceProp prop;
     EIGSOL_CUDA(cudaGetDeviceProperties(&prop, device));
     sm_count = prop.multiProcessorCount;
+    {
+        // the device's stream-ordered pool keeps what an ingest frees (up to EIGSOL_B200_POOL_KEEP_MB, default 16 GB of
+        // the 180) so that the next upload of a matrix does not pay the driver for its buffers again
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) {
+            uint64_t keep = uint64_t(std::max(0, env_int("EIGSOL_B200_POOL_KEEP_MB", 16384))) << 20;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        cudaGetLastError();
+    }
     EIGSOL_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     EIGSOL_CUDA(cudaEventCreate(&ev0));
     EIGSOL_CUDA(cudaEventCreate(&ev1));
@@ -353,6 +365,7 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     d_scal.alloc(kRing * 4 * sizeof(double));
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
+    gemv_tail = env_int("EIGSOL_B200_GEMV_TAIL", 0) ? 1 : 0;
     h_state.alloc(sizeof(PowerState));
 }
 
@@ -669,9 +682,10 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         // rest; as soon as outer + inner have landed the expansion, the sort by row and the row-pointer scan run on
         // the device UNDER the values upload; only the final gather waits for the values.
         DevBuf d_outer, d_inner, d_cvals, d_col, d_iota, d_perm, d_keys, d_flags, d_tmp, d_tmp2;
-        d_outer.alloc_raw(sizeof(int32_t) * size_t(cols + 1));
-        d_inner.alloc_raw(sizeof(int32_t) * nz);
-        d_cvals.alloc_raw(nz * s);
+        d_outer.alloc_pooled(sizeof(int32_t) * size_t(cols + 1), stream);
+        d_inner.alloc_pooled(sizeof(int32_t) * nz, stream);
+        d_cvals.alloc_pooled(nz * s, stream);
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));  // the uploader threads write from their own streams
         StagedUploader up;
         up.add(d_outer.p, outer, sizeof(int32_t) * size_t(cols + 1));
         const size_t index_jobs = up.add(d_inner.p, inner, sizeof(int32_t) * size_t(nnz));
@@ -688,22 +702,22 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         plan_exchange();
         setup_peer();
         csr.cols = ext_len;
-        d_rowptr.alloc(sizeof(int32_t) * size_t(rows + 1));  // zero-filled: the row histogram
-        d_colidx.alloc_raw(sizeof(int32_t) * nz);
-        d_vals.alloc_raw(nz * s);
-        d_col.alloc_raw(sizeof(int32_t) * nz);
-        d_iota.alloc_raw(sizeof(int32_t) * nz);
-        d_perm.alloc_raw(sizeof(int32_t) * nz);
-        d_keys.alloc_raw(sizeof(int32_t) * nz);
+        d_rowptr.alloc_pooled(sizeof(int32_t) * size_t(rows + 1), stream, true);  // zero-filled: the row histogram
+        d_colidx.alloc_pooled(sizeof(int32_t) * nz, stream);
+        d_vals.alloc_pooled(nz * s, stream);
+        d_col.alloc_pooled(sizeof(int32_t) * nz, stream);
+        d_iota.alloc_pooled(sizeof(int32_t) * nz, stream);
+        d_perm.alloc_pooled(sizeof(int32_t) * nz, stream);
+        d_keys.alloc_pooled(sizeof(int32_t) * nz, stream);
         d_flags.alloc(64);
         int end_bit = 1;
         while (end_bit < 31 && (int64_t(1) << end_bit) < rows) ++end_bit;
         size_t tb = 0, tb2 = 0;
         EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb, d_inner.as<int32_t>(), d_keys.as<int32_t>(),
                                                     d_iota.as<int32_t>(), d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
-        d_tmp.alloc_raw(tb);
+        d_tmp.alloc_pooled(tb, stream);
         EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(rows + 1), stream));
-        d_tmp2.alloc_raw(tb2);
+        d_tmp2.alloc_pooled(tb2, stream);
         tr.mark_async("ingest: remaining allocs");
         up.wait_prefix();
         tr.mark_async("ingest: outer + inner on the device");
@@ -959,9 +973,10 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     local_nnz = nnz;
     const size_t s = size_t(ss());
     const size_t nz = size_t(std::max<int64_t>(nnz, 1));
-    d_rowptr.alloc(sizeof(int32_t) * size_t(nloc + 1));
-    d_colidx.alloc(sizeof(int32_t) * nz);
-    d_vals.alloc(nz * s);
+    d_rowptr.alloc_pooled(sizeof(int32_t) * size_t(nloc + 1), stream);
+    d_colidx.alloc_pooled(sizeof(int32_t) * nz, stream, nnz == 0);
+    d_vals.alloc_pooled(nz * s, stream, nnz == 0);
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));  // the uploader threads write from their own streams
     StagedUploader up;
     up.add(d_rowptr.p, rowptr, sizeof(int32_t) * size_t(nloc + 1));
     up.add(d_colidx.p, colidx + base, sizeof(int32_t) * size_t(nnz));
@@ -990,8 +1005,8 @@ void MatrixImpl::finish_rows_on_device() {
     halo.peer_count.assign(size_t(nranks), 0);
     halo.peer_off.assign(size_t(nranks) + 1, 0);
     if (nnz > 0) {
-        d_mark.alloc(sizeof(int32_t) * size_t(n));
-        d_pos.alloc(sizeof(int32_t) * size_t(n));
+        d_mark.alloc_pooled(sizeof(int32_t) * size_t(n), stream, true);
+        d_pos.alloc_pooled(sizeof(int32_t) * size_t(n), stream);
         rows_mark_kernel<<<gnz, B, 0, stream>>>(d_colidx.as<int32_t>(), nnz, n, lo, hi, d_mark.as<int32_t>(), d_flags.as<int>());
         size_t tb = 0;
         EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, d_mark.as<int32_t>(), d_pos.as<int32_t>(), int(n), stream));
@@ -1213,10 +1228,14 @@ void MatrixImpl::set_kernel(int kernel_, int lanes_) {
         d_window.alloc(sizeof(int32_t) * w.size());
         d_window.upload(w.data(), sizeof(int32_t) * w.size(), stream);
         EIGSOL_CUDA(cudaStreamSynchronize(stream));
-        if (dtype)
-            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, window_smem));
-        else
-            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, window_smem));
+        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+        if (dtype) {
+            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double2, 256, false>, attr, window_smem));
+            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double2, 256, true>, attr, window_smem));
+        } else {
+            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double, 256, false>, attr, window_smem));
+            EIGSOL_CUDA(cudaFuncSetAttribute(spmv_csr_window_kernel<double, 256, true>, attr, window_smem));
+        }
     } else {
         lanes_ = 0;
     }
@@ -1284,24 +1303,27 @@ template <class K> static int occupancy(K kern, int block, size_t smem = 0) {
     return std::max(nb, 1);
 }
 
-template <class S> static int sparse_occupancy(int kernel, int lanes, int window_smem) {
+template <class S, bool PEER> static int sparse_occupancy_t(int kernel, int lanes, int window_smem) {
     constexpr int B = 256;
     switch (kernel) {
-        case K_CSR_WINDOW: return occupancy(spmv_csr_window_kernel<S, B>, B, size_t(window_smem));
-        case K_CSR_SCALAR: return occupancy(spmv_csr_scalar_kernel<S, B>, B);
-        case K_CSR_STREAM: return occupancy(spmv_csr_stream_kernel<S, B>, B);
+        case K_CSR_WINDOW: return occupancy(spmv_csr_window_kernel<S, B, PEER>, B, size_t(window_smem));
+        case K_CSR_SCALAR: return occupancy(spmv_csr_scalar_kernel<S, B, PEER>, B);
+        case K_CSR_STREAM: return occupancy(spmv_csr_stream_kernel<S, B, PEER>, B);
         case K_SELL:
-            return lanes == 2 ? occupancy(spmv_sell_kernel<S, 2, B>, B) : occupancy(spmv_sell_kernel<S, 1, B>, B);
+            return lanes == 2 ? occupancy(spmv_sell_kernel<S, 2, B, PEER>, B) : occupancy(spmv_sell_kernel<S, 1, B, PEER>, B);
         case K_CSR_VECTOR:
             switch (lanes) {
-                case 2: return occupancy(spmv_csr_vector_kernel<S, 2, B>, B);
-                case 4: return occupancy(spmv_csr_vector_kernel<S, 4, B>, B);
-                case 8: return occupancy(spmv_csr_vector_kernel<S, 8, B>, B);
-                case 16: return occupancy(spmv_csr_vector_kernel<S, 16, B>, B);
-                default: return occupancy(spmv_csr_vector_kernel<S, 32, B>, B);
+                case 2: return occupancy(spmv_csr_vector_kernel<S, 2, B, PEER>, B);
+                case 4: return occupancy(spmv_csr_vector_kernel<S, 4, B, PEER>, B);
+                case 8: return occupancy(spmv_csr_vector_kernel<S, 8, B, PEER>, B);
+                case 16: return occupancy(spmv_csr_vector_kernel<S, 16, B, PEER>, B);
+                default: return occupancy(spmv_csr_vector_kernel<S, 32, B, PEER>, B);
             }
     }
     return 1;
+}
+template <class S> static int sparse_occupancy(int kernel, int lanes, int window_smem, bool peer) {
+    return peer ? sparse_occupancy_t<S, true>(kernel, lanes, window_smem) : sparse_occupancy_t<S, false>(kernel, lanes, window_smem);
 }
 
 void MatrixImpl::configure_launch() {
@@ -1319,7 +1341,8 @@ void MatrixImpl::configure_launch() {
         d_tile_ticket.alloc(sizeof(unsigned) * size_t(ntiles));
         stored_bytes = s * lda * ext_len + s * (ext_len + nloc) + 2 * s * int64_t(nseg) * lda;
     } else {
-        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes, window_smem) : sparse_occupancy<double>(kernel, lanes, window_smem);
+        const bool peer = xmode == MODE_PEER;
+        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes, window_smem, peer) : sparse_occupancy<double>(kernel, lanes, window_smem, peer);
         const int resident = sm_count * occ;
         int64_t need = 1;
         switch (kernel) {
@@ -1411,36 +1434,40 @@ static void launch_pdl(bool pdl, cudaStream_t st, void (*kern)(KArgs...), dim3 g
     EIGSOL_CUDA(cudaLaunchKernelEx(&cfg, kern, KArgs(args)...));
 }
 
-template <class S> static void launch_sparse(MatrixImpl& m, int ph) {
+template <class S, bool PEER> static void launch_sparse_t(MatrixImpl& m, int ph) {
     constexpr int B = 256;
     IterArgs<S> it = m.iter_args<S>();
     CsrView<S> A{int32_t(m.nloc), m.d_rowptr.as<int32_t>(), m.d_colidx.as<int32_t>(), m.d_vals.as<S>()};
     const dim3 g(m.grid), b(B);
     cudaStream_t st = m.stream;
     switch (m.kernel) {
-        case K_CSR_SCALAR: launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B>, g, b, 0, A, it, ph); break;
+        case K_CSR_SCALAR: launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B, PEER>, g, b, 0, A, it, ph); break;
         case K_CSR_WINDOW:
-            launch_pdl(m.pdl, st, spmv_csr_window_kernel<S, B>, g, b, size_t(m.window_smem), A, m.d_window.as<int2>(), it, ph);
+            launch_pdl(m.pdl, st, spmv_csr_window_kernel<S, B, PEER>, g, b, size_t(m.window_smem), A, m.d_window.as<int2>(), it, ph);
             break;
-        case K_CSR_STREAM: launch_pdl(m.pdl, st, spmv_csr_stream_kernel<S, B>, g, b, 0, A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
+        case K_CSR_STREAM: launch_pdl(m.pdl, st, spmv_csr_stream_kernel<S, B, PEER>, g, b, 0, A, m.d_rowblk.as<int32_t>(), m.nblk, it, ph); break;
         case K_SELL: {
             SellView<S> V{int32_t(m.nloc), int32_t(m.sell_nslices), m.d_sell_off.as<int64_t>(), m.d_sell_col.as<int32_t>(),
                           m.d_sell_val.as<S>()};
-            if (m.lanes == 2) launch_pdl(m.pdl, st, spmv_sell_kernel<S, 2, B>, g, b, 0, V, it, ph);
-            else launch_pdl(m.pdl, st, spmv_sell_kernel<S, 1, B>, g, b, 0, V, it, ph);
+            if (m.lanes == 2) launch_pdl(m.pdl, st, spmv_sell_kernel<S, 2, B, PEER>, g, b, 0, V, it, ph);
+            else launch_pdl(m.pdl, st, spmv_sell_kernel<S, 1, B, PEER>, g, b, 0, V, it, ph);
             break;
         }
         case K_CSR_VECTOR:
             switch (m.lanes) {
-                case 2: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 2, B>, g, b, 0, A, it, ph); break;
-                case 4: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 4, B>, g, b, 0, A, it, ph); break;
-                case 8: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 8, B>, g, b, 0, A, it, ph); break;
-                case 16: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 16, B>, g, b, 0, A, it, ph); break;
-                default: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 32, B>, g, b, 0, A, it, ph); break;
+                case 2: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 2, B, PEER>, g, b, 0, A, it, ph); break;
+                case 4: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 4, B, PEER>, g, b, 0, A, it, ph); break;
+                case 8: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 8, B, PEER>, g, b, 0, A, it, ph); break;
+                case 16: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 16, B, PEER>, g, b, 0, A, it, ph); break;
+                default: launch_pdl(m.pdl, st, spmv_csr_vector_kernel<S, 32, B, PEER>, g, b, 0, A, it, ph); break;
             }
             break;
         default: throw StateError("no sparse kernel selected");
     }
+}
+template <class S> static void launch_sparse(MatrixImpl& m, int ph) {
+    if (m.xmode == MODE_PEER) launch_sparse_t<S, true>(m, ph);
+    else launch_sparse_t<S, false>(m, ph);
 }
 
 template <class S> static void launch_dense(MatrixImpl& m, int ph) {
@@ -1448,7 +1475,14 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
-    launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B>, dim3(m.grid), dim3(B), 0, A, it, ph);
+    const dim3 g(m.grid), b(B);
+    if (m.xmode == MODE_PEER) {
+        if (m.gemv_tail) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 1>, g, b, 0, A, it, ph);
+        else launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 0>, g, b, 0, A, it, ph);
+    } else {
+        if (m.gemv_tail) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 1>, g, b, 0, A, it, ph);
+        else launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 0>, g, b, 0, A, it, ph);
+    }
 }
 
 void MatrixImpl::launch_matvec(int phase) {
@@ -2360,10 +2394,10 @@ extern "C" int eigsol_b200_hbm_probe(int64_t plane_bytes, int planes, int reps, 
         return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: hbm probe takes 1, 4, 8 or 12 read planes");
     return guarded([&] {
         require_device();
-        const int64_t n2 = plane_bytes / 16;
+        const int64_t n4 = plane_bytes / 32;
         DevBuf in, out;
-        in.alloc(size_t(n2) * 16 * size_t(planes));
-        out.alloc(size_t(n2) * 16);
+        in.alloc(size_t(n4) * 32 * size_t(planes));
+        out.alloc(size_t(n4) * 32);
         int dev = 0, sms = 148;
         EIGSOL_CUDA(cudaGetDevice(&dev));
         EIGSOL_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -2372,18 +2406,18 @@ extern "C" int eigsol_b200_hbm_probe(int64_t plane_bytes, int planes, int reps, 
         cudaEvent_t e0, e1;
         EIGSOL_CUDA(cudaEventCreate(&e0));
         EIGSOL_CUDA(cudaEventCreate(&e1));
-        const int grid = sms * 8;
+        const int grid = sms * std::max(1, env_int("EIGSOL_B200_PROBE_CTAS_PER_SM", 4));
         auto launch = [&] {
             switch (planes) {
-                case 1: read_mix_kernel<1><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
-                case 4: read_mix_kernel<4><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
-                case 8: read_mix_kernel<8><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
-                default: read_mix_kernel<12><<<grid, 256, 0, st>>>(in.as<double2>(), n2, out.as<double2>()); break;
+                case 1: read_mix_kernel<1><<<grid, 256, 0, st>>>(in.as<double>(), n4, out.as<double>()); break;
+                case 4: read_mix_kernel<4><<<grid, 256, 0, st>>>(in.as<double>(), n4, out.as<double>()); break;
+                case 8: read_mix_kernel<8><<<grid, 256, 0, st>>>(in.as<double>(), n4, out.as<double>()); break;
+                default: read_mix_kernel<12><<<grid, 256, 0, st>>>(in.as<double>(), n4, out.as<double>()); break;
             }
         };
         for (int w = 0; w < 3; ++w) launch();
         double best = 0.0, sum = 0.0;
-        const double bytes = double(n2) * 16.0 * double(planes + 1);
+        const double bytes = double(n4) * 32.0 * double(planes + 1);
         for (int r = 0; r < reps; ++r) {
             EIGSOL_CUDA(cudaEventRecord(e0, st));
             launch();

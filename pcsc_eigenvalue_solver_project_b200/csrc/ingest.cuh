@@ -18,6 +18,7 @@
 
 #include <atomic>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <cub/device/device_radix_sort.cuh>
@@ -73,7 +74,17 @@ struct PinnedPool {
 // work that needs only those can start while the rest is still in flight); finish() joins and returns the first CUDA
 // error seen.  download = true reverses the direction (device -> pinned -> host array).
 struct StagedUploader {
-    static constexpr size_t kChunk = PinnedPool::kBytes;
+    // bytes per job: small enough that the first DMA starts early and the tail is short, large enough that the per-job
+    // cost (one cudaMemcpyAsync + one event) vanishes; EIGSOL_B200_UPLOAD_CHUNK_MB in [1, 16], default 4
+    static size_t chunk_bytes() {
+        static const size_t c = [] {
+            const char* e = std::getenv("EIGSOL_B200_UPLOAD_CHUNK_MB");
+            long mb = e && *e ? std::atol(e) : 4;
+            mb = mb < 1 ? 1 : (mb > 16 ? 16 : mb);
+            return size_t(mb) << 20;
+        }();
+        return c;
+    }
     struct Job {
         char* dst;
         const char* src;
@@ -95,9 +106,10 @@ struct StagedUploader {
             if (t.joinable()) t.join();
     }
     size_t add(void* dst, const void* src, size_t bytes) {
-        for (size_t off = 0; off < bytes; off += kChunk)
+        const size_t chunk = chunk_bytes();
+        for (size_t off = 0; off < bytes; off += chunk)
             jobs.push_back(Job{static_cast<char*>(dst) + off, static_cast<const char*>(src) + off,
-                               std::min(kChunk, bytes - off)});
+                               std::min(chunk, bytes - off)});
         return jobs.size();
     }
     void worker(int device) {

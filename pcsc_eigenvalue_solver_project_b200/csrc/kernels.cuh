@@ -347,17 +347,23 @@ template <class S> struct IterArgs {
     const uint8_t* deferred; // MODE_PEER: per work unit, 1 = reads halo entries (needs the halo wait first); may be null
     int serpentine;          // odd launches walk the work units backwards (what was touched last is re-read first: L2)
     int unit_start;          // rotation of the unit walk (see walk_units)
-    int halo_base;           // MODE_PEER: first halo index of the vector buffers (peers write there WHILE this kernel
-                             // runs, so those entries are read with coherent loads, see ld_x); INT32_MAX otherwise
+    int halo_base;           // MODE_PEER: first halo index of the vector buffers; INT32_MAX otherwise (diagnostics)
 };
 
-// Gather of one x entry.  Own entries were written by the previous launch of this GPU: read-only for this
-// kernel's lifetime, so they take the non-coherent path (ld.global.nc through L1).  Halo entries (index >=
-// halo_base, MODE_PEER only) are stored by peer GPUs while this kernel is already running and are read only
-// after the acquire of the owner's flag: PTX allows ld.global.nc only for data nobody writes during the kernel,
-// so they use ld.global.cg (L2, coherent with the peers' NVLink stores).
-template <class S> __device__ __forceinline__ S ld_x(const S* u, int idx, int halo_base) {
-    return idx < halo_base ? Sc<S>::ldg(u + idx) : Sc<S>::ldcg(u + idx);
+// Gather of one x entry, per exchange mode (the matvec kernels are compiled twice, PEER = false / true):
+//   PEER = false (one GPU, NCCL mode): nothing writes the input vector while the kernel runs -> the non-coherent
+//       read-only path (ld.global.nc via __ldg), which also lets the compiler batch the gathers of an unrolled row.
+//   PEER = true (MODE_PEER): the halo segment of the input vector is stored by peer GPUs WHILE this kernel is already
+//       running and is read only after the acquire of the owner's flag.  PTX defines ld.global.nc only for data nobody
+//       writes during the kernel's lifetime, so this variant uses plain (coherent-at-acquire, L1-cached) loads for every
+//       gather and carries no __restrict__ on the vector.  No halo line can sit in L1 before the flag: the halo starts
+//       on a 128-byte boundary (nloc_pad) and nothing reads it before the wait.
+template <class S, bool PEER> struct XPtr { typedef const S* __restrict__ type; };
+template <class S> struct XPtr<S, true> { typedef const S* type; };
+
+template <class S, bool PEER> __device__ __forceinline__ S ld_x(const S* u, int idx) {
+    if constexpr (PEER) return u[idx];
+    else return Sc<S>::ldg(u + idx);
 }
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
@@ -697,7 +703,7 @@ __device__ __forceinline__ void walk_units(const IterArgs<S>& it, const LaunchCt
 // warp but every fetched sector is consumed by the following loop trips out of L1.
 // Work unit = BLOCK consecutive rows.
 // =================================================================================================
-template <class S, int BLOCK>
+template <class S, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
     pdl_prologue();
     if (blockIdx.x == 0) {
@@ -708,9 +714,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* u = ring_buf<S>(it, c.in);
+    typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     const int nunits = (A.rows + BLOCK - 1) / BLOCK;
     walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nunits, [&](int unit) {
@@ -718,8 +723,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
         if (row < A.rows) {
             const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
             S acc = Sc<S>::zero();
-            for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), ld_x<S>(u, __ldg(A.colidx + p), hb));
-            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, are, aim, qn);
+            for (int p = p0; p < p1; ++p) Sc<S>::mac(acc, __ldg(A.vals + p), ld_x<S, PEER>(u, __ldg(A.colidx + p)));
+            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), ld_x<S, PEER>(u, row), out, row, are, aim, qn);
         }
     });
     cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
@@ -730,7 +735,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, It
 // instruction reads LANES consecutive values / indices; partial sums meet in a shuffle tree.
 // Work unit = BLOCK / LANES consecutive rows (one CTA-wide step).
 // =================================================================================================
-template <class S, int LANES, int BLOCK>
+template <class S, int LANES, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
     pdl_prologue();
     if (blockIdx.x == 0) {
@@ -741,9 +746,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* u = ring_buf<S>(it, c.in);
+    typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     constexpr int RPU = BLOCK / LANES;  // rows per unit
     const int sub = threadIdx.x % LANES;
@@ -754,12 +758,12 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_vector_kernel(CsrView<S> A, It
         if (row < A.rows) {
             const int p0 = __ldg(A.rowptr + row), p1 = __ldg(A.rowptr + row + 1);
             for (int p = p0 + sub; p < p1; p += LANES)
-                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), ld_x<S>(u, ld_stream_s32(A.colidx + p), hb));
+                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), ld_x<S, PEER>(u, ld_stream_s32(A.colidx + p)));
         }
 #pragma unroll
         for (int d = LANES / 2; d > 0; d >>= 1) Sc<S>::add(acc, Sc<S>::shfl_down(acc, d, LANES));
         if (sub == 0 && row < A.rows)
-            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + row), out, row, are, aim, qn);
+            row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), ld_x<S, PEER>(u, row), out, row, are, aim, qn);
     });
     cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
 }
@@ -777,7 +781,7 @@ template <> struct StreamCfg<double> { static constexpr int TILE = 4096; };   //
 template <> struct StreamCfg<double2> { static constexpr int TILE = 2048; };  // 32 KB of products
 constexpr int kStreamMaxRows = 512;
 
-template <class S, int BLOCK>
+template <class S, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, const int32_t* __restrict__ rowblk,
                                                                 int nblk, IterArgs<S> it, int phase) {
     pdl_prologue();
@@ -793,9 +797,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* u = ring_buf<S>(it, c.in);
+    typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     const double* vals_d = reinterpret_cast<const double*>(A.vals);
     walk_units<S>(it, c, blockIdx.x - 1, gridDim.x - 1, nblk, [&](int b) {
@@ -809,7 +812,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
             // one long row: CTA-strided partial sums, then a CTA reduction (real and imaginary parts).
             S acc = Sc<S>::zero();
             for (int p = p0 + threadIdx.x; p < p1; p += BLOCK)
-                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), ld_x<S>(u, ld_stream_s32(A.colidx + p), hb));
+                Sc<S>::mac(acc, ld_stream_val<S>(A.vals + p), ld_x<S, PEER>(u, ld_stream_s32(A.colidx + p)));
             double ar, ai = 0.0, dummy = 0.0;
             if constexpr (Sc<S>::is_complex) {
                 ar = acc.x;
@@ -822,7 +825,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                 S z;
                 if constexpr (Sc<S>::is_complex) z = make_double2(ar * c.s, ai * c.s);
                 else z = ar * c.s;
-                row_epilogue<S>(sends, z, Sc<S>::ldg(u + r0), out, r0, are, aim, qn);
+                row_epilogue<S>(sends, z, ld_x<S, PEER>(u, r0), out, r0, are, aim, qn);
             }
         } else {
             for (int e = base + 2 * threadIdx.x; e < p1; e += 2 * BLOCK) {
@@ -836,15 +839,15 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_stream_kernel(CsrView<S> A, co
                     v0 = vv.x;
                     v1 = vv.y;
                 }
-                prod[e - base] = Sc<S>::mul(v0, ld_x<S>(u, cc.x, hb));
-                prod[e - base + 1] = Sc<S>::mul(v1, ld_x<S>(u, cc.y, hb));
+                prod[e - base] = Sc<S>::mul(v0, ld_x<S, PEER>(u, cc.x));
+                prod[e - base + 1] = Sc<S>::mul(v1, ld_x<S, PEER>(u, cc.y));
             }
             __syncthreads();
             for (int i = threadIdx.x; i < nr; i += BLOCK) {
                 S acc = Sc<S>::zero();
                 const int q1 = srow[i + 1] - base;
                 for (int q = srow[i] - base; q < q1; ++q) Sc<S>::add(acc, prod[q]);
-                row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), Sc<S>::ldg(u + r0 + i), out, r0 + i, are, aim, qn);
+                row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), ld_x<S, PEER>(u, r0 + i), out, r0 + i, are, aim, qn);
             }
         }
         __syncthreads();
@@ -888,7 +891,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
     }
 }
 
-template <class S, int BLOCK>
+template <class S, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, const int2* __restrict__ win, IterArgs<S> it,
                                                                 int phase) {
     extern __shared__ __align__(128) unsigned char window_smem[];
@@ -904,9 +907,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, co
     if (threadIdx.x == 0) mbar_init(&bar, 1);
     load_sends<S>(it, c, sends);  // ends with a CTA barrier: the mbarrier is initialised for everyone
     S* xs = reinterpret_cast<S*>(window_smem);
-    const S* u = ring_buf<S>(it, c.in);
+    typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     unsigned parity = 0;
     const int nunits = (A.rows + BLOCK - 1) / BLOCK;
@@ -928,11 +930,11 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, co
             for (int p = p0; p < p1; ++p) {
                 const int col = __ldg(A.colidx + p);
                 const unsigned k = unsigned(col - w.x);
-                const S x = k < unsigned(w.y) ? xs[k] : ld_x<S>(u, col, hb);
+                const S x = k < unsigned(w.y) ? xs[k] : ld_x<S, PEER>(u, col);
                 Sc<S>::mac(acc, __ldg(A.vals + p), x);
             }
             const unsigned kd = unsigned(row - w.x);
-            const S own = kd < unsigned(w.y) ? xs[kd] : Sc<S>::ldg(u + row);
+            const S own = kd < unsigned(w.y) ? xs[kd] : ld_x<S, PEER>(u, row);
             row_epilogue<S>(sends, Sc<S>::scale(acc, c.s), own, out, row, are, aim, qn);
         }
         __syncthreads();  // everyone is done reading the window before the next bulk copy lands in it
@@ -947,7 +949,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_csr_window_kernel(CsrView<S> A, co
 // indices, and for stencil-like rows the x gathers of neighbouring lanes fall into the same lines.
 // No shared memory, no block barrier in the main loop.  Work unit = one slice (per warp).
 // =================================================================================================
-template <class S, int R, int BLOCK>
+template <class S, int R, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArgs<S> it, int phase) {
     pdl_prologue();
     if (blockIdx.x == 0) {
@@ -958,9 +960,8 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
-    const S* u = ring_buf<S>(it, c.in);
+    typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int hb = it.halo_base;
     double are = 0.0, aim = 0.0, qn = 0.0;
     const int lane = threadIdx.x & 31;
     const int gwarp = ((blockIdx.x - 1) * BLOCK + threadIdx.x) >> 5;
@@ -995,7 +996,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
             }
 #pragma unroll
             for (int r = 0; r < R; ++r)
-                if (col[r] >= 0) Sc<S>::mac(acc[r], v[r], ld_x<S>(u, col[r], hb));
+                if (col[r] >= 0) Sc<S>::mac(acc[r], v[r], ld_x<S, PEER>(u, col[r]));
             vp += 32 * R;
             cp += 32 * R;
         }
@@ -1003,7 +1004,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 #pragma unroll
         for (int r = 0; r < R; ++r)
             if (row + r < A.rows)
-                row_epilogue<S>(sends, Sc<S>::scale(acc[r], c.s), Sc<S>::ldg(u + row + r), out, row + r, are, aim, qn);
+                row_epilogue<S>(sends, Sc<S>::scale(acc[r], c.s), ld_x<S, PEER>(u, row + r), out, row + r, are, aim, qn);
     });
     cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
 }
@@ -1016,7 +1017,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 // =================================================================================================
 constexpr int kGemvChunk = 512;  // columns of x staged per pass
 
-template <class S, int BLOCK>
+template <class S, int BLOCK, bool PEER, int TAIL>
 __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, IterArgs<S> it, int phase) {
     pdl_prologue();
     if (blockIdx.x == 0) {
@@ -1032,9 +1033,8 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);
     if (it.mode == MODE_PEER) halo_wait_cta<S>(it, c);  // every row reads the whole halo
-    const S* u = ring_buf<S>(it, c.in);
+    typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int hb = it.halo_base;
     const int cta = blockIdx.x - 1;
     const int tile = cta / A.nseg, seg = cta % A.nseg;
     const int c0 = int(int64_t(A.cols) * seg / A.nseg), c1 = int(int64_t(A.cols) * (seg + 1) / A.nseg);
@@ -1046,7 +1046,7 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     for (int cb = c0; cb < c1; cb += kGemvChunk) {
         const int nc = min(kGemvChunk, c1 - cb);
         __syncthreads();
-        for (int j = threadIdx.x; j < nc; j += BLOCK) xs[j] = Sc<S>::scale(ld_x<S>(u, cb + j, hb), c.s);
+        for (int j = threadIdx.x; j < nc; j += BLOCK) xs[j] = Sc<S>::scale(ld_x<S, PEER>(u, cb + j), c.s);
         __syncthreads();
         if (live) {
             const S* col = A.a + int64_t(cb) * A.lda + r;
@@ -1077,32 +1077,45 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     __syncthreads();
     if (!s_tile_last) return;
     __threadfence();
-    // The tail of the launch: only the ntiles last CTAs are still running, so what matters is latency.  The segment
-    // partials (L2-resident) are fetched eight segments at a time -- 8 * R independent loads in flight per thread --
-    // and added in segment order (deterministic).
+    // The tail of the launch: only the ntiles last CTAs are still running, so what matters is latency.
     double are = 0.0, aim = 0.0, qn = 0.0;
-    if (live) {
-        S z[R];
+    if constexpr (TAIL == 0) {
+        // segment partials (L2-resident) added in segment order, one row after the other
 #pragma unroll
-        for (int k = 0; k < R; ++k) z[k] = Sc<S>::zero();
-        const S* pp = A.partial + r;
-        for (int s0 = 0; s0 < A.nseg; s0 += 8) {
-            S t[8][R];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const bool in = s0 + i < A.nseg;
-#pragma unroll
-                for (int k = 0; k < R; ++k)
-                    t[i][k] = in ? Sc<S>::ldcg(pp + int64_t(s0 + i) * A.lda + k) : Sc<S>::zero();
+        for (int k = 0; k < R; ++k) {
+            const int row = r + k;
+            if (row < A.rows) {
+                S z = Sc<S>::zero();
+                for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
+                row_epilogue<S>(sends, z, ld_x<S, PEER>(u, row), out, row, are, aim, qn);
             }
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int k = 0; k < R; ++k) Sc<S>::add(z[k], t[i][k]);
         }
+    } else {
+        // the same sums with the loads of four segments in flight per row (same order of additions)
+        if (live) {
+            S z[R];
 #pragma unroll
-        for (int k = 0; k < R; ++k)
-            if (r + k < A.rows) row_epilogue<S>(sends, z[k], Sc<S>::ldg(u + r + k), out, r + k, are, aim, qn);
+            for (int k = 0; k < R; ++k) z[k] = Sc<S>::zero();
+            const S* pp = A.partial + r;
+            int s0 = 0;
+            for (; s0 + 4 <= A.nseg; s0 += 4) {
+                S t[4][R];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int k = 0; k < R; ++k) t[i][k] = Sc<S>::ldcg(pp + int64_t(s0 + i) * A.lda + k);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int k = 0; k < R; ++k) Sc<S>::add(z[k], t[i][k]);
+            }
+            for (; s0 < A.nseg; ++s0)
+#pragma unroll
+                for (int k = 0; k < R; ++k) Sc<S>::add(z[k], Sc<S>::ldcg(pp + int64_t(s0) * A.lda + k));
+#pragma unroll
+            for (int k = 0; k < R; ++k)
+                if (r + k < A.rows) row_epilogue<S>(sends, z[k], ld_x<S, PEER>(u, r + k), out, r + k, are, aim, qn);
+        }
     }
     cta_finish<S, BLOCK>(it, c, are, aim, qn, tile);
 }

@@ -35,25 +35,51 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
+    bool pooled = false;
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes), pooled(o.pooled) { o.p = nullptr; o.bytes = 0; o.pooled = false; }
     DevBuf& operator=(DevBuf&& o) noexcept {
         if (this != &o) {
             release();
             p = o.p;
             bytes = o.bytes;
+            pooled = o.pooled;
             o.p = nullptr;
             o.bytes = 0;
+            o.pooled = false;
         }
         return *this;
     }
     ~DevBuf() { release(); }
     void release() {
-        if (p) cudaFree(p);
+        if (p) {
+            // pooled memory goes back to the device's stream-ordered pool (no device synchronisation, no driver
+            // round trip; the next ingest reuses it); callers only release buffers whose work has completed
+            if (pooled) cudaFreeAsync(p, cudaStreamPerThread);
+            else cudaFree(p);
+        }
         p = nullptr;
         bytes = 0;
+        pooled = false;
+    }
+    // Large, private (never shared with a peer GPU or another process) buffers: from the device's default
+    // stream-ordered memory pool.  No zero fill unless asked.  The memory may be used on OTHER streams only after
+    // `st` has been synchronised (or an event dependency) -- callers synchronise once after a batch of allocations.
+    void alloc_pooled(size_t n, cudaStream_t st, bool zero = false, size_t pad = 64) {
+        release();
+        bytes = n;
+        const cudaError_t e = cudaMallocAsync(&p, n + pad, st);
+        if (e != cudaSuccess) {  // no pool support (old driver / MPS quirk): plain allocation
+            cudaGetLastError();
+            p = nullptr;
+            if (zero) alloc(n, pad);
+            else alloc_raw(n, pad);
+            return;
+        }
+        pooled = true;
+        if (zero) EIGSOL_CUDA(cudaMemsetAsync(p, 0, n + pad, st));
     }
     // pad: extra zeroed bytes behind the payload so vector loads may over-read safely
     void alloc(size_t n, size_t pad = 64) {

@@ -44,12 +44,16 @@ def build(cfg):
         a = gen.dense_random_symmetric(n)
         dm = es.DeviceMatrix.from_matrix(es.Matrix(a))
         dt = np.float64
-    elif cfg[0] in "si" and cfg[1:].isdigit():
-        # s<k>: regular k-point stencil rows; i<k>: irregular rows, Poisson(k) entries (dispatch tuning)
+    elif cfg[0] in "si" and cfg[1:].rstrip("c").isdigit():
+        # s<k>: regular k-point stencil rows; i<k>: irregular rows, Poisson(k) entries (dispatch tuning);
+        # a trailing "c" makes the values complex (c128)
         n = 1 << 20
-        rp, ci, v = gen.banded_random_csr(n, int(cfg[1:]), 4096, seed=1, regular=cfg[0] == "s")
+        cplx = cfg.endswith("c")
+        rp, ci, v = gen.banded_random_csr(n, int(cfg[1:].rstrip("c")), 4096, seed=1, regular=cfg[0] == "s")
+        if cplx:
+            v = v + 1j * np.roll(v, 1)
         dm = es.DeviceMatrix.from_csr_rows(n, 0, rp, ci, v)
-        dt = np.float64
+        dt = np.complex128 if cplx else np.float64
     else:
         raise SystemExit(f"unknown config {cfg}")
     rng = np.random.default_rng(1)
@@ -79,7 +83,8 @@ def main():
             dm.step(10)
             best = min(dm.step(trips) for _ in range(3)) / trips
             r = dm.end(want_vector=False)
-            out = {"cfg": cfg, "kernel": info["kernel_name"], "lanes": lanes, "ms_per_trip": best,
+            out = {"cfg": cfg, "row_len_mean": info["row_len_mean"], "row_len_max": info["row_len_max"],
+                   "kernel": info["kernel_name"], "lanes": lanes, "ms_per_trip": best,
                    "it_per_s": 1e3 / best, "alg_GBps": info["alg_bytes"] / best / 1e6,
                    "stored_GBps": info["stored_bytes"] / best / 1e6, "grid": info["grid"], "lambda": repr(r.eigenvalue),
                    "set_kernel_s": round(tset, 2)}
