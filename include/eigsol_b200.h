@@ -133,6 +133,21 @@ EIGSOL_B200_API int eigsol_b200_power_dense(int dtype, int64_t rows, int64_t col
                                             double tolerance, void* x_out, double lambda_out[2],
                                             int* iterations_out, int* converged_out);
 
+/* The same two calls, but on success the device-resident matrix is handed to the caller (*keep_out; destroy it with
+ * eigsol_b200_matrix_destroy) instead of being freed: the first solve on a Matrix and its upload are ONE call (the start
+ * vector rides on the matrix upload), later solves call eigsol_b200_power_run on the kept handle.  This is what the
+ * drop-in Matrix cache uses.  keep_out == NULL is the plain one-shot call. */
+EIGSOL_B200_API int eigsol_b200_power_csc_keep(int dtype, int64_t rows, int64_t cols, const int32_t* outer,
+                                               const int32_t* inner, const void* values, const void* x0,
+                                               int max_iterations, double tolerance, void* x_out,
+                                               double lambda_out[2], int* iterations_out, int* converged_out,
+                                               eigsol_b200_matrix** keep_out);
+EIGSOL_B200_API int eigsol_b200_power_dense_keep(int dtype, int64_t rows, int64_t cols, const void* a,
+                                                 int64_t lda, const void* x0, int max_iterations,
+                                                 double tolerance, void* x_out, double lambda_out[2],
+                                                 int* iterations_out, int* converged_out,
+                                                 eigsol_b200_matrix** keep_out);
+
 /* ---- handle API: upload once, iterate many (device-resident Matrix; bench + repeated callers) -- */
 
 /* comm == NULL: the calling process owns the whole solve.  By default that is ONE GPU (the calling thread's

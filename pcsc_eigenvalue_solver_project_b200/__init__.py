@@ -140,6 +140,24 @@ class Matrix:
             self._a = np.asfortranarray(a).copy(order="F")  # stored by value, column-major (matrix.hpp:39-40)
             self._dtype = a.dtype
 
+    # Device-resident copy (the C++ drop-in does the same in eigsol/src/matrix/matrix.hpp): a Matrix
+    # can neither move nor be copied, so it can carry its uploaded copy; powerMethod(M) uploads once per Matrix.
+    # cast() hands out the stored (mutable) arrays: from then on the host copy may change behind our back, so the
+    # device copy is dropped and never cached again -- every later solve uploads what the host holds at that moment.
+    _dm = None
+    _cacheable = True
+
+    def _drop_device_copy(self):
+        if self._dm is not None:
+            self._dm.close()
+            self._dm = None
+
+    def __del__(self):
+        try:
+            self._drop_device_copy()
+        except Exception:
+            pass
+
     def __copy__(self):
         raise TypeError("Matrix is non-copyable by design")
 
@@ -164,6 +182,8 @@ class Matrix:
     def cast(self, kind: str, dtype):
         if (kind, np.dtype(dtype).type) != self.type():
             raise TypeError("bad cast")  # std::bad_cast
+        self._cacheable = False
+        self._drop_device_copy()
         if self._dense:
             return self._a
         return self._outer, self._inner, self._values
@@ -191,20 +211,28 @@ def powerMethod(M: Matrix, opts: SolverOptions | None = None, scalar=None, x0: n
     x0 = np.ascontiguousarray(x0, dtype=_capi.np_dtype(code))
     if x0.shape != (n,):
         raise ValueError("x0 must have length n")
+    if M._cacheable and M._dm is not None:
+        return M._dm.power(x0, opts)  # the Matrix is resident already: no upload
     x = np.empty(n, dtype=_capi.np_dtype(code))
     lam = np.zeros(2)
     iters, conv = C.c_int(0), C.c_int(0)
     L = _capi.lib()
+    # first solve on this Matrix: upload + solve in one call; the device copy is kept with the Matrix unless mutable
+    # access to its arrays was ever handed out (cast)
+    keep = C.c_void_p()
+    keep_ref = C.byref(keep) if M._cacheable else None
     if M.isDense():
         a = M._a
-        st = L.eigsol_b200_power_dense(code, n, ncols, _capi.ptr(a), a.strides[1] // a.itemsize if n > 1 else n,
-                                       _capi.ptr(x0), int(opts.maxIterations), float(opts.tolerance), _capi.ptr(x),
-                                       _capi.ptr(lam), C.byref(iters), C.byref(conv))
+        st = L.eigsol_b200_power_dense_keep(code, n, ncols, _capi.ptr(a), a.strides[1] // a.itemsize if n > 1 else n,
+                                            _capi.ptr(x0), int(opts.maxIterations), float(opts.tolerance), _capi.ptr(x),
+                                            _capi.ptr(lam), C.byref(iters), C.byref(conv), keep_ref)
     else:
-        st = L.eigsol_b200_power_csc(code, n, ncols, _capi.ptr(M._outer), _capi.ptr(M._inner), _capi.ptr(M._values),
-                                     _capi.ptr(x0), int(opts.maxIterations), float(opts.tolerance), _capi.ptr(x),
-                                     _capi.ptr(lam), C.byref(iters), C.byref(conv))
+        st = L.eigsol_b200_power_csc_keep(code, n, ncols, _capi.ptr(M._outer), _capi.ptr(M._inner), _capi.ptr(M._values),
+                                          _capi.ptr(x0), int(opts.maxIterations), float(opts.tolerance), _capi.ptr(x),
+                                          _capi.ptr(lam), C.byref(iters), C.byref(conv), keep_ref)
     _capi.check(st)
+    if keep.value:
+        M._dm = DeviceMatrix(keep, code, n, None)
     eig = complex(lam[0], lam[1]) if code == C128 else float(lam[0])
     return EigenResult(eig, x, int(iters.value), bool(conv.value))
 

@@ -22,7 +22,7 @@ KERNEL_NAMES = {0: "auto", 1: "csr_scalar", 2: "csr_vector", 3: "csr_stream", 4:
 # every symbol include/eigsol_b200.h declares (tests check the library exports all of them)
 EXPORTS = [
     "eigsol_b200_last_error", "eigsol_b200_device_count", "eigsol_b200_version",
-    "eigsol_b200_power_csc", "eigsol_b200_power_dense",
+    "eigsol_b200_power_csc", "eigsol_b200_power_dense", "eigsol_b200_power_csc_keep", "eigsol_b200_power_dense_keep",
     "eigsol_b200_matrix_create_csc", "eigsol_b200_matrix_create_csr_rows", "eigsol_b200_matrix_create_dense",
     "eigsol_b200_matrix_destroy", "eigsol_b200_matrix_get_info", "eigsol_b200_matrix_set_kernel",
     "eigsol_b200_power_run", "eigsol_b200_power_begin", "eigsol_b200_power_step", "eigsol_b200_power_end",
@@ -90,6 +90,8 @@ def lib():
         "eigsol_b200_version": (C.c_char_p, []),
         "eigsol_b200_power_csc": (i, [i, i64, i64, i32p, i32p, vp, vp, i, d, vp, dp, ip, ip]),
         "eigsol_b200_power_dense": (i, [i, i64, i64, vp, i64, vp, i, d, vp, dp, ip, ip]),
+        "eigsol_b200_power_csc_keep": (i, [i, i64, i64, i32p, i32p, vp, vp, i, d, vp, dp, ip, ip, C.POINTER(vp)]),
+        "eigsol_b200_power_dense_keep": (i, [i, i64, i64, vp, i64, vp, i, d, vp, dp, ip, ip, C.POINTER(vp)]),
         "eigsol_b200_matrix_create_csc": (i, [i, i64, i64, i32p, i32p, vp, vp, C.POINTER(vp)]),
         "eigsol_b200_matrix_create_csr_rows": (i, [i, i64, i64, i64, i32p, i32p, vp, vp, C.POINTER(vp)]),
         "eigsol_b200_matrix_create_dense": (i, [i, i64, i64, vp, i64, vp, C.POINTER(vp)]),

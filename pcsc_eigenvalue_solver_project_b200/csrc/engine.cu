@@ -247,6 +247,8 @@ struct MatrixImpl {
     int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
     int serpentine = 0;
     bool pdl = true;  // programmatic dependent launch of the matvec kernels
+    int spmv_prefetch = 0;  // EIGSOL_B200_SPMV_PREFETCH: csr_scalar work units per direction prefetched into L2 (kernels.cuh)
+    int gemv_prefetch = 0;  // EIGSOL_B200_GEMV_PREFETCH: columns per CTA pulled into L2 before the predecessor completes
     int gemv_tail = 0;  // EIGSOL_B200_GEMV_TAIL: combine variant of the dense kernel's last CTA per row tile
 
     // dense layout
@@ -309,6 +311,7 @@ struct MatrixImpl {
         a.serpentine = serpentine;
         a.unit_start = (xmode == MODE_PEER && have_deferred) ? unit_start : 0;
         a.halo_base = xmode == MODE_PEER ? int(nloc_pad) : INT32_MAX;
+        a.prefetch_units = spmv_prefetch;
         return a;
     }
     void alloc_vectors();
@@ -345,9 +348,7 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     } else {
         EIGSOL_CUDA(cudaGetDevice(&device));
     }
-    cudaDeviceProp prop;
-    EIGSOL_CUDA(cudaGetDeviceProperties(&prop, device));
-    sm_count = prop.multiProcessorCount;
+    EIGSOL_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));  // (cudaGetDeviceProperties costs ms)
     {
         // the device's stream-ordered pool keeps what an ingest frees (up to EIGSOL_B200_POOL_KEEP_MB, default 16 GB of
         // the 180) so that the next upload of a matrix does not pay the driver for its buffers again
@@ -366,15 +367,24 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
     gemv_tail = env_int("EIGSOL_B200_GEMV_TAIL", 0) ? 1 : 0;
+    spmv_prefetch = std::max(0, std::min(8, env_int("EIGSOL_B200_SPMV_PREFETCH", 0)));
+    gemv_prefetch = std::max(0, std::min(256, env_int("EIGSOL_B200_GEMV_PREFETCH", 16)));
     h_state.alloc(sizeof(PowerState));
 }
 
 void MatrixImpl::alloc_vectors() {
     nloc_pad = (nloc + 15) / 16 * 16;
     ext_len = nloc_pad + nhalo;
-    for (auto& b : buf)
-        if (!(b.p && b.bytes == size_t(ext_len) * ss())) b.alloc(size_t(ext_len) * ss(), 256);  // buf[0] may be in place already (preloaded x0)
-    d_xloc.alloc(size_t(std::max<int64_t>(nloc, 1)) * ss());
+    // one GPU: the vectors are private -> pool memory (no driver round trip on reuse); a group shares them with its peers
+    // (CUDA IPC / peer access), which needs plain allocations
+    for (auto& b : buf) {
+        if (b.p && b.bytes == size_t(ext_len) * ss()) continue;  // buf[0] may be in place already (preloaded x0)
+        if (nranks == 1) b.alloc_pooled(size_t(ext_len) * ss(), stream, true, 256);
+        else b.alloc(size_t(ext_len) * ss(), 256);
+    }
+    if (nranks == 1) d_xloc.alloc_pooled(size_t(std::max<int64_t>(nloc, 1)) * ss(), stream);
+    else d_xloc.alloc(size_t(std::max<int64_t>(nloc, 1)) * ss());
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
     if (nranks > 1 && !(comm && comm->local)) d_xglob.alloc(size_t(std::max<int64_t>(n, 1)) * ss());  // NCCL gather target
 }
 
@@ -692,7 +702,8 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         up.add(d_cvals.p, values, size_t(nnz) * s);
         if (preload_x0) {
             // one-shot call: the start vector rides on the same upload (begin() then finds it in place)
-            buf[0].alloc(size_t((rows + 15) / 16 * 16) * s, 256);
+            buf[0].alloc_pooled(size_t((rows + 15) / 16 * 16) * s, stream, true, 256);
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
             up.add(buf[0].p, preload_x0, size_t(rows) * s);
         }
         up.start(device, upload_threads(nranks), index_jobs);
@@ -1277,9 +1288,21 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
     stats.mean = stats.max = stats.min = double(n);
     lda = (nloc + 15) / 16 * 16;
     if (lda == 0) lda = 16;
-    d_dense.alloc(size_t(lda) * size_t(std::max<int64_t>(ext_len, 1)) * ss());
     const char* src = static_cast<const char*>(a);
     const size_t s = size_t(ss());
+    if (nranks == 1 && lda == n && lda_host == n && size_t(n) * size_t(n) * s >= (size_t(32) << 20)) {
+        // the whole matrix is one contiguous column-major block with the device's leading dimension: several host
+        // threads through pinned staging (a pageable cudaMemcpy2D moves ~12 GB/s, this ~40)
+        d_dense.alloc_pooled(size_t(lda) * size_t(ext_len) * s, stream);
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        StagedUploader up;
+        up.add(d_dense.p, src, size_t(n) * size_t(n) * s);
+        EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+        set_kernel(K_GEMV, 0);
+        compute_prescale();
+        return;
+    }
+    d_dense.alloc(size_t(lda) * size_t(std::max<int64_t>(ext_len, 1)) * ss());
     auto copy_cols = [&](int64_t gcol0, int64_t ncols, int64_t ecol0) {
         if (ncols <= 0 || nloc <= 0) return;
         EIGSOL_CUDA(cudaMemcpy2DAsync(d_dense.as<char>() + size_t(ecol0) * size_t(lda) * s, size_t(lda) * s,
@@ -1474,7 +1497,7 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     constexpr int B = 256;
     IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
-                   m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>()};
+                   m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>(), m.gemv_prefetch};
     const dim3 g(m.grid), b(B);
     if (m.xmode == MODE_PEER) {
         if (m.gemv_tail) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 1>, g, b, 0, A, it, ph);
@@ -2113,10 +2136,12 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
             ++g_matrices_created;
             return int(EIGSOL_B200_OK);
         }
+        Trace tr0;
         h->one.reset(new MatrixImpl);
         MatrixImpl& m = *h->one;
         m.init_common(dtype, comm ? &comm->impl : nullptr);
         m.n = rows;
+        tr0.mark_async("create: handle + streams");
         if (m.nranks == 1 && env_int("EIGSOL_B200_DEVICE_INGEST", 1)) {
             m.preload_x0 = g_preload_x0;
             m.init_sparse_device_csc(rows, cols, outer, inner, values);
@@ -2237,8 +2262,10 @@ int eigsol_b200_matrix_create_dense(int dtype, int64_t rows, int64_t cols, const
 int eigsol_b200_matrix_destroy(eigsol_b200_matrix* m) {
     if (!m) return EIGSOL_B200_OK;
     return guarded([&] {
+        Trace tr;
         if (m->one) cudaSetDevice(m->one->device);
         delete m;
+        tr.mark_async("destroy");
         return int(EIGSOL_B200_OK);
     });
 }
@@ -2442,32 +2469,59 @@ extern "C" int eigsol_b200_hbm_probe(int64_t plane_bytes, int planes, int reps, 
 // ---- one-shot entry points ------------------------------------------------------------------------
 extern "C" {
 
-int eigsol_b200_power_csc(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
-                          const void* values, const void* x0, int max_iterations, double tolerance, void* x_out,
-                          double lambda_out[2], int* iterations_out, int* converged_out) {
+// Solve and, if keep_out != NULL, hand the device-resident matrix to the caller instead of destroying it: the FIRST
+// solve on a matrix and its upload are one call (the start vector rides on the matrix upload), later solves use
+// eigsol_b200_power_run on *keep_out.
+int eigsol_b200_power_csc_keep(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                               const void* values, const void* x0, int max_iterations, double tolerance, void* x_out,
+                               double lambda_out[2], int* iterations_out, int* converged_out, eigsol_b200_matrix** keep_out) {
+    if (keep_out) *keep_out = nullptr;
     eigsol_b200_matrix* m = nullptr;
     g_preload_x0 = x0;  // the start vector goes up together with the matrix (single GPU)
     int e = eigsol_b200_matrix_create_csc(dtype, rows, cols, outer, inner, values, nullptr, &m);
     g_preload_x0 = nullptr;
     if (e) return e;
     e = eigsol_b200_power_run(m, x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
+    if (!e && keep_out) {
+        *keep_out = m;
+        return e;
+    }
     const std::string keep = g_last_error;
     eigsol_b200_matrix_destroy(m);
     if (e) g_last_error = keep;
     return e;
 }
 
-int eigsol_b200_power_dense(int dtype, int64_t rows, int64_t cols, const void* a, int64_t lda, const void* x0,
-                            int max_iterations, double tolerance, void* x_out, double lambda_out[2],
-                            int* iterations_out, int* converged_out) {
+int eigsol_b200_power_dense_keep(int dtype, int64_t rows, int64_t cols, const void* a, int64_t lda, const void* x0,
+                                 int max_iterations, double tolerance, void* x_out, double lambda_out[2],
+                                 int* iterations_out, int* converged_out, eigsol_b200_matrix** keep_out) {
+    if (keep_out) *keep_out = nullptr;
     eigsol_b200_matrix* m = nullptr;
     int e = eigsol_b200_matrix_create_dense(dtype, rows, cols, a, lda, nullptr, &m);
     if (e) return e;
     e = eigsol_b200_power_run(m, x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
+    if (!e && keep_out) {
+        *keep_out = m;
+        return e;
+    }
     const std::string keep = g_last_error;
     eigsol_b200_matrix_destroy(m);
     if (e) g_last_error = keep;
     return e;
+}
+
+int eigsol_b200_power_csc(int dtype, int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner,
+                          const void* values, const void* x0, int max_iterations, double tolerance, void* x_out,
+                          double lambda_out[2], int* iterations_out, int* converged_out) {
+    return eigsol_b200_power_csc_keep(dtype, rows, cols, outer, inner, values, x0, max_iterations, tolerance, x_out,
+                                      lambda_out, iterations_out, converged_out, nullptr);
+}
+
+int eigsol_b200_power_dense(int dtype, int64_t rows, int64_t cols, const void* a, int64_t lda, const void* x0,
+                            int max_iterations, double tolerance, void* x_out, double lambda_out[2],
+                            int* iterations_out, int* converged_out) {
+    return eigsol_b200_power_dense_keep(dtype, rows, cols, a, lda, x0, max_iterations, tolerance, x_out, lambda_out,
+                                        iterations_out, converged_out, nullptr);
 }
 
 // ---- multi-GPU group ------------------------------------------------------------------------------

@@ -133,6 +133,7 @@ template <class S> struct DenseView {
     int32_t ntiles;     // row tiles
     S* partial;         // [nseg][lda] partial sums
     unsigned* tile_ticket;  // [ntiles]
+    int32_t prefetch_cols;  // columns of the CTA's own segment pulled into L2 while the previous launch drains
 };
 
 // -------------------------------------------------------------------------------------------------
@@ -348,6 +349,8 @@ template <class S> struct IterArgs {
     int serpentine;          // odd launches walk the work units backwards (what was touched last is re-read first: L2)
     int unit_start;          // rotation of the unit walk (see walk_units)
     int halo_base;           // MODE_PEER: first halo index of the vector buffers; INT32_MAX otherwise (diagnostics)
+    int prefetch_units;      // csr_scalar: work units (per walking direction) whose matrix entries a CTA pulls into L2
+                             // between becoming resident and the completion of the previous launch
 };
 
 // Gather of one x entry, per exchange mode (the matvec kernels are compiled twice, PEER = false / true):
@@ -437,6 +440,15 @@ __device__ __forceinline__ void cta_sum3(double& a, double& b, double& c, double
 __device__ __forceinline__ void pdl_prologue() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+// The two halves, for kernels that use the time between becoming resident and the predecessor's completion: the
+// matrix is read-only across launches, so its first bytes can be pulled into L2 (prefetch_l2) while the previous
+// launch's tail -- which leaves HBM idle -- is still running; only the vector depends on the predecessor.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// one bulk L2 prefetch (TMA engine, no register or shared-memory destination); bytes a multiple of 16, 16-byte aligned
+__device__ __forceinline__ void prefetch_l2(const void* p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -705,7 +717,26 @@ __device__ __forceinline__ void walk_units(const IterArgs<S>& it, const LaunchCt
 // =================================================================================================
 template <class S, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
-    pdl_prologue();
+    pdl_launch_dependents();
+    if (it.prefetch_units > 0 && blockIdx.x != 0 && threadIdx.x < 2 * it.prefetch_units) {
+        // The matrix does not change between launches: while the previous launch drains (HBM is idle in its tail), one
+        // thread per unit pulls the entries of the first unit(s) this CTA will walk -- in either direction, the
+        // direction is only known after the wait -- into L2 with bulk prefetches.
+        const int nunits_ = (A.rows + BLOCK - 1) / BLOCK;
+        const int k = threadIdx.x >> 1;
+        const int i = int(blockIdx.x) - 1 + k * (int(gridDim.x) - 1);
+        if (i < nunits_) {
+            int unit = ((threadIdx.x & 1) ? nunits_ - 1 - i : i) + it.unit_start;
+            if (unit >= nunits_) unit -= nunits_;
+            const int r0 = unit * BLOCK, r1 = min(r0 + BLOCK, A.rows);
+            const int64_t p0 = __ldg(A.rowptr + r0) & ~3, p1 = (int64_t(__ldg(A.rowptr + r1)) + 3) & ~int64_t(3);
+            if (p1 > p0) {
+                prefetch_l2(A.vals + p0, unsigned((p1 - p0) * int64_t(sizeof(S))));
+                prefetch_l2(A.colidx + p0, unsigned((p1 - p0) * 4));
+            }
+        }
+    }
+    pdl_wait();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
@@ -1019,13 +1050,24 @@ constexpr int kGemvChunk = 512;  // columns of x staged per pass
 
 template <class S, int BLOCK, bool PEER, int TAIL>
 __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, IterArgs<S> it, int phase) {
-    pdl_prologue();
+    constexpr int R = Sc<S>::is_complex ? 1 : 2;
+    constexpr int RT = BLOCK * R;
+    pdl_launch_dependents();
+    if (blockIdx.x != 0 && A.prefetch_cols > 0 && int(threadIdx.x) < A.prefetch_cols) {
+        // resident while the previous launch drains: thread j pulls column j of this CTA's piece of A into L2
+        const int cta_ = blockIdx.x - 1;
+        const int tile_ = cta_ / A.nseg, seg_ = cta_ % A.nseg;
+        const int c0_ = int(int64_t(A.cols) * seg_ / A.nseg), c1_ = int(int64_t(A.cols) * (seg_ + 1) / A.nseg);
+        const int64_t r0_ = int64_t(tile_) * RT;
+        const int64_t nr = A.lda - r0_ < RT ? A.lda - r0_ : RT;
+        const int col = c0_ + int(threadIdx.x);
+        if (col < c1_ && nr > 0) prefetch_l2(A.a + int64_t(col) * A.lda + r0_, unsigned(nr * int64_t(sizeof(S))));
+    }
+    pdl_wait();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
     }
-    constexpr int R = Sc<S>::is_complex ? 1 : 2;
-    constexpr int RT = BLOCK * R;
     __shared__ __align__(16) S xs[kGemvChunk];
     __shared__ int s_tile_last;
     __shared__ SendSm sends;

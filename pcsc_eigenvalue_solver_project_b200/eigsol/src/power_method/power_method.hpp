@@ -74,10 +74,17 @@ inline void check(int status) {
     if (status != EIGSOL_B200_OK) raise_last_error();
 }
 
-// Uploads A once; the returned handle owns the device copy.
+// The device loop on A.  First solve on a matrix (`slot` empty): upload and solve in ONE library call -- the start
+// vector rides on the matrix upload -- and the device copy is kept in `slot`; later solves run on the resident copy.
 template <typename Mat>
-std::shared_ptr<void> upload(const Mat& A) {
+void run_on(const Mat& A, std::shared_ptr<void>& slot, const typename Mat::Scalar* x0, const SolverOptions& opts,
+            typename Mat::Scalar* x, double lambda[2], int* iterations, int* converged) {
     using Scalar = typename Mat::Scalar;
+    if (slot) {
+        check(eigsol_b200_power_run(static_cast<eigsol_b200_matrix*>(slot.get()), x0, opts.maxIterations, opts.tolerance, x,
+                                    lambda, iterations, converged));
+        return;
+    }
     eigsol_b200_matrix* h = nullptr;
     if constexpr (is_sparse_v<Mat>) {
         using Canon = Eigen::SparseMatrix<Scalar, Eigen::ColMajor, int>;
@@ -91,20 +98,21 @@ std::shared_ptr<void> upload(const Mat& A) {
             tmp.makeCompressed();
             csc = &tmp;
         }
-        check(eigsol_b200_matrix_create_csc(dtype_code<Scalar>, csc->rows(), csc->cols(), csc->outerIndexPtr(),
-                                            csc->innerIndexPtr(), csc->valuePtr(), nullptr, &h));
+        check(eigsol_b200_power_csc_keep(dtype_code<Scalar>, csc->rows(), csc->cols(), csc->outerIndexPtr(),
+                                         csc->innerIndexPtr(), csc->valuePtr(), x0, opts.maxIterations, opts.tolerance, x,
+                                         lambda, iterations, converged, &h));
     } else {
         using Canon = Eigen::Matrix<Scalar, Eigen::Dynamic, Eigen::Dynamic>;
         if constexpr (std::is_same_v<Mat, Canon>) {
-            check(eigsol_b200_matrix_create_dense(dtype_code<Scalar>, A.rows(), A.cols(), A.data(), A.outerStride(),
-                                                  nullptr, &h));
+            check(eigsol_b200_power_dense_keep(dtype_code<Scalar>, A.rows(), A.cols(), A.data(), A.outerStride(), x0,
+                                               opts.maxIterations, opts.tolerance, x, lambda, iterations, converged, &h));
         } else {
             const Canon tmp(A);
-            check(eigsol_b200_matrix_create_dense(dtype_code<Scalar>, tmp.rows(), tmp.cols(), tmp.data(),
-                                                  tmp.outerStride(), nullptr, &h));
+            check(eigsol_b200_power_dense_keep(dtype_code<Scalar>, tmp.rows(), tmp.cols(), tmp.data(), tmp.outerStride(), x0,
+                                               opts.maxIterations, opts.tolerance, x, lambda, iterations, converged, &h));
         }
     }
-    return std::shared_ptr<void>(h, [](void* p) { eigsol_b200_matrix_destroy(static_cast<eigsol_b200_matrix*>(p)); });
+    slot = std::shared_ptr<void>(h, [](void* p) { eigsol_b200_matrix_destroy(static_cast<eigsol_b200_matrix*>(p)); });
 }
 
 // Shape checks + x0 exactly as the reference (:52-62), then the device loop on `slot`'s matrix
@@ -122,20 +130,19 @@ EigenResult<typename Mat::Scalar> solve(const Mat& A, const SolverOptions& opts,
         x0s.normalize();
         Vector<Wide> x0 = x0s.template cast<Wide>();
         x0.normalize();
-        if (!slot) {
-            if constexpr (is_sparse_v<Mat>) {
-                const Eigen::SparseMatrix<Wide, Eigen::ColMajor, int> wide = A.template cast<Wide>();
-                slot = upload(wide);
-            } else {
-                const Eigen::Matrix<Wide, Eigen::Dynamic, Eigen::Dynamic> wide = A.template cast<Wide>();
-                slot = upload(wide);
-            }
-        }
         Vector<Wide> x(n);
         double lambda[2] = {0.0, 0.0};
         int iterations = 0, converged = 0;
-        check(eigsol_b200_power_run(static_cast<eigsol_b200_matrix*>(slot.get()), x0.data(), opts.maxIterations,
-                                    opts.tolerance, x.data(), lambda, &iterations, &converged));
+        if (slot) {
+            run_on(Eigen::Matrix<Wide, Eigen::Dynamic, Eigen::Dynamic>(), slot, x0.data(), opts, x.data(), lambda, &iterations,
+                   &converged);  // resident already: the matrix argument is not looked at
+        } else if constexpr (is_sparse_v<Mat>) {
+            const Eigen::SparseMatrix<Wide, Eigen::ColMajor, int> wide = A.template cast<Wide>();
+            run_on(wide, slot, x0.data(), opts, x.data(), lambda, &iterations, &converged);
+        } else {
+            const Eigen::Matrix<Wide, Eigen::Dynamic, Eigen::Dynamic> wide = A.template cast<Wide>();
+            run_on(wide, slot, x0.data(), opts, x.data(), lambda, &iterations, &converged);
+        }
         Scalar value;
         if constexpr (std::is_same_v<Scalar, float>) value = static_cast<float>(lambda[0]);
         else value = Scalar(static_cast<float>(lambda[0]), static_cast<float>(lambda[1]));
@@ -145,12 +152,10 @@ EigenResult<typename Mat::Scalar> solve(const Mat& A, const SolverOptions& opts,
     } else {
         Vector<Scalar> x0 = Vector<Scalar>::Random(n);
         x0.normalize();
-        if (!slot) slot = upload(A);
         Vector<Scalar> x(n);
         double lambda[2] = {0.0, 0.0};
         int iterations = 0, converged = 0;
-        check(eigsol_b200_power_run(static_cast<eigsol_b200_matrix*>(slot.get()), x0.data(), opts.maxIterations,
-                                    opts.tolerance, x.data(), lambda, &iterations, &converged));
+        run_on(A, slot, x0.data(), opts, x.data(), lambda, &iterations, &converged);
         Scalar value;
         if constexpr (std::is_same_v<Scalar, double>) value = lambda[0];
         else value = Scalar(lambda[0], lambda[1]);
