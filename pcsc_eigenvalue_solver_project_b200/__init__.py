@@ -28,7 +28,7 @@ from ._capi import (C128, F64, KERNEL_AUTO, KERNEL_CSR_SCALAR, KERNEL_CSR_STREAM
 
 __all__ = ["Matrix", "SolverOptions", "EigenResult", "powerMethod", "power_method", "DeviceMatrix", "Comm",
            "BlockEigenResult", "blockPowerMethod", "random_block",
-           "random_unit", "srand", "device_count", "hbm_probe", "EigsolB200Error", "readMatrixFromFile",
+           "random_unit", "srand", "device_count", "hbm_probe", "matrices_created", "EigsolB200Error", "readMatrixFromFile",
            "writeMatrixBinary", "readMatrixBinary"]
 
 
@@ -63,6 +63,11 @@ class BlockEigenResult:
 
 def device_count() -> int:
     return int(_capi.lib().eigsol_b200_device_count())
+
+
+def matrices_created() -> int:
+    """Matrix handles (= uploads of a whole matrix) this process has created so far."""
+    return int(_capi.lib().eigsol_b200_matrices_created())
 
 
 def hbm_probe(plane_bytes: int = 128 << 20, planes: int = 12, reps: int = 20) -> tuple[float, float]:

@@ -441,3 +441,37 @@ def test_extreme_matrix_scales(orc, scale):
     x0 = orc.random_unit(48, np.float64, seed=4)
     r = es.powerMethod(es.Matrix(a), es.SolverOptions(40, -1.0), x0=x0)
     check_result(r, orc.power_dense(a, x0, 40, -1.0))
+
+
+# ---- device-resident Matrix cache of the Python mirror (the C++ one: tests/dropin/device_cache_test.cpp) ----
+def test_matrix_device_cache_uploads_once_and_never_goes_stale(orc):
+    g = 20
+    n = g * g
+    rowptr, colidx, vals = gen.laplacian_2d(g)
+    outer, inner, cv = csc_of(rowptr, colidx, vals)
+    x0 = orc.random_unit(n, np.float64, seed=5)
+    M = es.Matrix(((n, n), outer, inner, cv))
+    before = es.matrices_created()
+    r1 = es.powerMethod(M, es.SolverOptions(30, -1.0), x0=x0)
+    r2 = es.powerMethod(M, es.SolverOptions(30, -1.0), x0=x0)
+    r3 = es.powerMethod(M, es.SolverOptions(45, -1.0), x0=x0)
+    assert es.matrices_created() - before == 1          # one upload for three solves
+    assert r1.eigenvalue == r2.eigenvalue and np.array_equal(r1.eigenvector, r2.eigenvector)
+    check_result(r3, orc.power_csc((n, n), outer, inner, cv, x0, 45, -1.0))
+    # cast() hands out the stored arrays: the device copy is dropped and never cached again
+    o, i, v = M.cast("sparse", np.float64)
+    r4 = es.powerMethod(M, es.SolverOptions(30, -1.0), x0=x0)
+    assert r4.eigenvalue == r1.eigenvalue
+    v[:] = v * 2.0                                       # edit through the reference kept from cast()
+    before = es.matrices_created()
+    r5 = es.powerMethod(M, es.SolverOptions(30, -1.0), x0=x0)
+    assert es.matrices_created() - before == 1          # uploaded afresh
+    assert abs(r5.eigenvalue - 2.0 * r1.eigenvalue) <= 1e-12 * abs(r5.eigenvalue)
+    # dense
+    a = gen.dense_random_symmetric(40, seed=2)
+    D = es.Matrix(a)
+    x0 = orc.random_unit(40, np.float64, seed=6)
+    before = es.matrices_created()
+    es.powerMethod(D, es.SolverOptions(10, -1.0), x0=x0)
+    check_result(es.powerMethod(D, es.SolverOptions(25, -1.0), x0=x0), orc.power_dense(a, x0, 25, -1.0))
+    assert es.matrices_created() - before == 1

@@ -55,6 +55,16 @@ def main():
               if ms < best:
                   best, best_mine = ms, mine
           info = dm.info()
+          if os.environ.get("EIGSOL_B200_PEER_STATS") and world > 1:
+              dm.peer_stats()  # reset
+              ms1 = dm.step(320)
+              ps = dm.peer_stats()
+              la = max(ps["control_launches"], 1)
+              print(f"# peer_stats cfg={cfg_name} g={g} rank={rank} us/trip={ms1 / 320 * 1e3:.2f} "
+                    f"control_wait_us/launch={ps['control_wait_ns'] / la / 1e3:.2f} halo_warps/launch={ps['halo_warps'] / la:.1f} "
+                    f"waiting_warps/launch={ps['halo_waiting_warps'] / la:.1f} "
+                    f"mean_halo_wait_us={(ps['halo_wait_ns'] / max(ps['halo_waiting_warps'], 1)) / 1e3:.2f} "
+                    f"max_halo_wait_us={ps['halo_wait_max_ns'] / 1e3:.2f}", flush=True)
           r = dm.end(want_vector=False)
           if world > 1 and os.environ.get("LAT_PER_RANK"):
               print(f"# cfg={cfg_name} g={g} rank={rank} us={best_mine / 320 * 1e3:.2f}", flush=True)
