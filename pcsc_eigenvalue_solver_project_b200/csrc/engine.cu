@@ -247,9 +247,8 @@ struct MatrixImpl {
     int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
     int serpentine = 0;
     bool pdl = true;  // programmatic dependent launch of the matvec kernels
-    int spmv_prefetch = 0;  // EIGSOL_B200_SPMV_PREFETCH: csr_scalar work units per direction prefetched into L2 (kernels.cuh)
-    int gemv_prefetch = 0;  // EIGSOL_B200_GEMV_PREFETCH: columns per CTA pulled into L2 before the predecessor completes
-    int gemv_tail = 0;  // EIGSOL_B200_GEMV_TAIL: combine variant of the dense kernel's last CTA per row tile
+    int gemv_map = 0;  // EIGSOL_B200_GEMV_MAP: 1 = row tiles of one column segment are neighbouring CTAs
+    int gemv_var = 0;  // EIGSOL_B200_GEMV_VAR: streaming loop variant of the dense kernel (kernels.cuh)
 
     // dense layout
     DevBuf d_dense, d_dense_partial, d_tile_ticket;
@@ -311,7 +310,6 @@ struct MatrixImpl {
         a.serpentine = serpentine;
         a.unit_start = (xmode == MODE_PEER && have_deferred) ? unit_start : 0;
         a.halo_base = xmode == MODE_PEER ? int(nloc_pad) : INT32_MAX;
-        a.prefetch_units = spmv_prefetch;
         return a;
     }
     void alloc_vectors();
@@ -366,9 +364,8 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     d_scal.alloc(kRing * 4 * sizeof(double));
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
-    gemv_tail = env_int("EIGSOL_B200_GEMV_TAIL", 0) ? 1 : 0;
-    spmv_prefetch = std::max(0, std::min(8, env_int("EIGSOL_B200_SPMV_PREFETCH", 0)));
-    gemv_prefetch = std::max(0, std::min(256, env_int("EIGSOL_B200_GEMV_PREFETCH", 16)));
+    gemv_var = env_int("EIGSOL_B200_GEMV_VAR", 0) ? 1 : 0;
+    gemv_map = env_int("EIGSOL_B200_GEMV_MAP", 0) ? 1 : 0;
     h_state.alloc(sizeof(PowerState));
 }
 
@@ -1497,13 +1494,13 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     constexpr int B = 256;
     IterArgs<S> it = m.iter_args<S>();
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
-                   m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>(), m.gemv_prefetch};
+                   m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>(), m.gemv_map};
     const dim3 g(m.grid), b(B);
     if (m.xmode == MODE_PEER) {
-        if (m.gemv_tail) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 1>, g, b, 0, A, it, ph);
+        if (m.gemv_var) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 1>, g, b, 0, A, it, ph);
         else launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 0>, g, b, 0, A, it, ph);
     } else {
-        if (m.gemv_tail) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 1>, g, b, 0, A, it, ph);
+        if (m.gemv_var) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 1>, g, b, 0, A, it, ph);
         else launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 0>, g, b, 0, A, it, ph);
     }
 }

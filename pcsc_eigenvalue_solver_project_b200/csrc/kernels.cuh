@@ -133,7 +133,7 @@ template <class S> struct DenseView {
     int32_t ntiles;     // row tiles
     S* partial;         // [nseg][lda] partial sums
     unsigned* tile_ticket;  // [ntiles]
-    int32_t prefetch_cols;  // columns of the CTA's own segment pulled into L2 while the previous launch drains
+    int32_t tile_major;     // launch order of the CTAs: 1 = row tiles of one column segment are neighbours
 };
 
 // -------------------------------------------------------------------------------------------------
@@ -349,8 +349,6 @@ template <class S> struct IterArgs {
     int serpentine;          // odd launches walk the work units backwards (what was touched last is re-read first: L2)
     int unit_start;          // rotation of the unit walk (see walk_units)
     int halo_base;           // MODE_PEER: first halo index of the vector buffers; INT32_MAX otherwise (diagnostics)
-    int prefetch_units;      // csr_scalar: work units (per walking direction) whose matrix entries a CTA pulls into L2
-                             // between becoming resident and the completion of the previous launch
 };
 
 // Gather of one x entry, per exchange mode (the matvec kernels are compiled twice, PEER = false / true):
@@ -717,26 +715,7 @@ __device__ __forceinline__ void walk_units(const IterArgs<S>& it, const LaunchCt
 // =================================================================================================
 template <class S, int BLOCK, bool PEER>
 __global__ void __launch_bounds__(BLOCK) spmv_csr_scalar_kernel(CsrView<S> A, IterArgs<S> it, int phase) {
-    pdl_launch_dependents();
-    if (it.prefetch_units > 0 && blockIdx.x != 0 && threadIdx.x < 2 * it.prefetch_units) {
-        // The matrix does not change between launches: while the previous launch drains (HBM is idle in its tail), one
-        // thread per unit pulls the entries of the first unit(s) this CTA will walk -- in either direction, the
-        // direction is only known after the wait -- into L2 with bulk prefetches.
-        const int nunits_ = (A.rows + BLOCK - 1) / BLOCK;
-        const int k = threadIdx.x >> 1;
-        const int i = int(blockIdx.x) - 1 + k * (int(gridDim.x) - 1);
-        if (i < nunits_) {
-            int unit = ((threadIdx.x & 1) ? nunits_ - 1 - i : i) + it.unit_start;
-            if (unit >= nunits_) unit -= nunits_;
-            const int r0 = unit * BLOCK, r1 = min(r0 + BLOCK, A.rows);
-            const int64_t p0 = __ldg(A.rowptr + r0) & ~3, p1 = (int64_t(__ldg(A.rowptr + r1)) + 3) & ~int64_t(3);
-            if (p1 > p0) {
-                prefetch_l2(A.vals + p0, unsigned((p1 - p0) * int64_t(sizeof(S))));
-                prefetch_l2(A.colidx + p0, unsigned((p1 - p0) * 4));
-            }
-        }
-    }
-    pdl_wait();
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
@@ -1048,27 +1027,22 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 // =================================================================================================
 constexpr int kGemvChunk = 512;  // columns of x staged per pass
 
-template <class S, int BLOCK, bool PEER, int TAIL>
+// VAR 0: x staged 512 columns at a time, 8 column loads in flight per thread.  VAR 1: 64 columns, 4 loads in flight
+// (fewer registers).  A.tile_major selects which neighbours a CTA has in the launch order: 0 = the column segments of
+// one row tile, 1 = the row tiles of one column segment (adjacent CTAs then read adjacent 4 KB pieces of the SAME
+// columns, i.e. whole contiguous columns between them).
+template <class S, int BLOCK, bool PEER, int VAR>
 __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, IterArgs<S> it, int phase) {
-    constexpr int R = Sc<S>::is_complex ? 1 : 2;
-    constexpr int RT = BLOCK * R;
-    pdl_launch_dependents();
-    if (blockIdx.x != 0 && A.prefetch_cols > 0 && int(threadIdx.x) < A.prefetch_cols) {
-        // resident while the previous launch drains: thread j pulls column j of this CTA's piece of A into L2
-        const int cta_ = blockIdx.x - 1;
-        const int tile_ = cta_ / A.nseg, seg_ = cta_ % A.nseg;
-        const int c0_ = int(int64_t(A.cols) * seg_ / A.nseg), c1_ = int(int64_t(A.cols) * (seg_ + 1) / A.nseg);
-        const int64_t r0_ = int64_t(tile_) * RT;
-        const int64_t nr = A.lda - r0_ < RT ? A.lda - r0_ : RT;
-        const int col = c0_ + int(threadIdx.x);
-        if (col < c1_ && nr > 0) prefetch_l2(A.a + int64_t(col) * A.lda + r0_, unsigned(nr * int64_t(sizeof(S))));
-    }
-    pdl_wait();
+    pdl_prologue();
     if (blockIdx.x == 0) {
         control_cta<S, BLOCK>(it, true);
         return;
     }
-    __shared__ __align__(16) S xs[kGemvChunk];
+    constexpr int R = Sc<S>::is_complex ? 1 : 2;
+    constexpr int RT = BLOCK * R;
+    constexpr int CHUNK = VAR == 0 ? kGemvChunk : 64;
+    constexpr int UNROLL = VAR == 0 ? 8 : 4;
+    __shared__ __align__(16) S xs[CHUNK];
     __shared__ int s_tile_last;
     __shared__ SendSm sends;
     LaunchCtx c;
@@ -1078,21 +1052,22 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     typename XPtr<S, PEER>::type u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
     const int cta = blockIdx.x - 1;
-    const int tile = cta / A.nseg, seg = cta % A.nseg;
+    const int tile = A.tile_major ? cta % A.ntiles : cta / A.nseg;
+    const int seg = A.tile_major ? cta / A.ntiles : cta % A.nseg;
     const int c0 = int(int64_t(A.cols) * seg / A.nseg), c1 = int(int64_t(A.cols) * (seg + 1) / A.nseg);
     const int r = tile * RT + threadIdx.x * R;
     const bool live = r < A.lda;  // lda is even and rows beyond A.rows are zero-filled on the device
     S acc[R];
 #pragma unroll
     for (int k = 0; k < R; ++k) acc[k] = Sc<S>::zero();
-    for (int cb = c0; cb < c1; cb += kGemvChunk) {
-        const int nc = min(kGemvChunk, c1 - cb);
+    for (int cb = c0; cb < c1; cb += CHUNK) {
+        const int nc = min(CHUNK, c1 - cb);
         __syncthreads();
         for (int j = threadIdx.x; j < nc; j += BLOCK) xs[j] = Sc<S>::scale(ld_x<S, PEER>(u, cb + j), c.s);
         __syncthreads();
         if (live) {
             const S* col = A.a + int64_t(cb) * A.lda + r;
-#pragma unroll 8
+#pragma unroll UNROLL
             for (int j = 0; j < nc; ++j) {
                 if constexpr (R == 2) {
                     const double2 a = ld_stream_f64x2(reinterpret_cast<const double*>(col));
@@ -1119,44 +1094,15 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     __syncthreads();
     if (!s_tile_last) return;
     __threadfence();
-    // The tail of the launch: only the ntiles last CTAs are still running, so what matters is latency.
+    // The tail of the launch: the last CTA of a row tile adds the segment partials (L2-resident) in segment order.
     double are = 0.0, aim = 0.0, qn = 0.0;
-    if constexpr (TAIL == 0) {
-        // segment partials (L2-resident) added in segment order, one row after the other
 #pragma unroll
-        for (int k = 0; k < R; ++k) {
-            const int row = r + k;
-            if (row < A.rows) {
-                S z = Sc<S>::zero();
-                for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
-                row_epilogue<S>(sends, z, ld_x<S, PEER>(u, row), out, row, are, aim, qn);
-            }
-        }
-    } else {
-        // the same sums with the loads of four segments in flight per row (same order of additions)
-        if (live) {
-            S z[R];
-#pragma unroll
-            for (int k = 0; k < R; ++k) z[k] = Sc<S>::zero();
-            const S* pp = A.partial + r;
-            int s0 = 0;
-            for (; s0 + 4 <= A.nseg; s0 += 4) {
-                S t[4][R];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int k = 0; k < R; ++k) t[i][k] = Sc<S>::ldcg(pp + int64_t(s0 + i) * A.lda + k);
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int k = 0; k < R; ++k) Sc<S>::add(z[k], t[i][k]);
-            }
-            for (; s0 < A.nseg; ++s0)
-#pragma unroll
-                for (int k = 0; k < R; ++k) Sc<S>::add(z[k], Sc<S>::ldcg(pp + int64_t(s0) * A.lda + k));
-#pragma unroll
-            for (int k = 0; k < R; ++k)
-                if (r + k < A.rows) row_epilogue<S>(sends, z[k], ld_x<S, PEER>(u, r + k), out, r + k, are, aim, qn);
+    for (int k = 0; k < R; ++k) {
+        const int row = r + k;
+        if (row < A.rows) {
+            S z = Sc<S>::zero();
+            for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
+            row_epilogue<S>(sends, z, ld_x<S, PEER>(u, row), out, row, are, aim, qn);
         }
     }
     cta_finish<S, BLOCK>(it, c, are, aim, qn, tile);

@@ -79,7 +79,10 @@ struct DevBuf {
             return;
         }
         pooled = true;
+        // the pad is ALWAYS zero: kernels over-read index arrays by a vector width and use what they read as a gather
+        // index (recycled pool memory holds garbage)
         if (zero) EIGSOL_CUDA(cudaMemsetAsync(p, 0, n + pad, st));
+        else if (pad) EIGSOL_CUDA(cudaMemsetAsync(static_cast<char*>(p) + n, 0, pad, st));
     }
     // pad: extra zeroed bytes behind the payload so vector loads may over-read safely
     void alloc(size_t n, size_t pad = 64) {
@@ -96,6 +99,7 @@ struct DevBuf {
         release();
         bytes = n;
         EIGSOL_CUDA(cudaMalloc(&p, n + pad));
+        if (pad) EIGSOL_CUDA(cudaMemset(static_cast<char*>(p) + n, 0, pad));  // over-read area: always zero
     }
     void upload(const void* src, size_t n, cudaStream_t s) {
         if (n) EIGSOL_CUDA(cudaMemcpyAsync(p, src, n, cudaMemcpyHostToDevice, s));
