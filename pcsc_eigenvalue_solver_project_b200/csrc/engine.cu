@@ -247,6 +247,7 @@ struct MatrixImpl {
     int unit_start = 0;  // rotation of the unit walk: middle of the longest halo-free run of units
     int serpentine = 0;
     bool pdl = true;  // programmatic dependent launch of the matvec kernels
+    int scalar_block = 256;  // EIGSOL_B200_SCALAR_BLOCK: threads per CTA (= rows per work unit) of csr_scalar
     int gemv_map = 0;  // EIGSOL_B200_GEMV_MAP: 1 = row tiles of one column segment are neighbouring CTAs
     int gemv_var = 0;  // EIGSOL_B200_GEMV_VAR: streaming loop variant of the dense kernel (kernels.cuh)
 
@@ -364,7 +365,8 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     d_scal.alloc(kRing * 4 * sizeof(double));
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
-    gemv_var = env_int("EIGSOL_B200_GEMV_VAR", 0) ? 1 : 0;
+    scalar_block = env_int("EIGSOL_B200_SCALAR_BLOCK", 256) == 128 ? 128 : 256;
+    gemv_var = std::max(0, std::min(2, env_int("EIGSOL_B200_GEMV_VAR", 0)));
     gemv_map = env_int("EIGSOL_B200_GEMV_MAP", 0) ? 1 : 0;
     h_state.alloc(sizeof(PowerState));
 }
@@ -1323,11 +1325,12 @@ template <class K> static int occupancy(K kern, int block, size_t smem = 0) {
     return std::max(nb, 1);
 }
 
-template <class S, bool PEER> static int sparse_occupancy_t(int kernel, int lanes, int window_smem) {
+template <class S, bool PEER> static int sparse_occupancy_t(int kernel, int lanes, int window_smem, int block) {
     constexpr int B = 256;
     switch (kernel) {
         case K_CSR_WINDOW: return occupancy(spmv_csr_window_kernel<S, B, PEER>, B, size_t(window_smem));
-        case K_CSR_SCALAR: return occupancy(spmv_csr_scalar_kernel<S, B, PEER>, B);
+        case K_CSR_SCALAR:
+            return block == 128 ? occupancy(spmv_csr_scalar_kernel<S, 128, PEER>, 128) : occupancy(spmv_csr_scalar_kernel<S, B, PEER>, B);
         case K_CSR_STREAM: return occupancy(spmv_csr_stream_kernel<S, B, PEER>, B);
         case K_SELL:
             return lanes == 2 ? occupancy(spmv_sell_kernel<S, 2, B, PEER>, B) : occupancy(spmv_sell_kernel<S, 1, B, PEER>, B);
@@ -1342,15 +1345,17 @@ template <class S, bool PEER> static int sparse_occupancy_t(int kernel, int lane
     }
     return 1;
 }
-template <class S> static int sparse_occupancy(int kernel, int lanes, int window_smem, bool peer) {
-    return peer ? sparse_occupancy_t<S, true>(kernel, lanes, window_smem) : sparse_occupancy_t<S, false>(kernel, lanes, window_smem);
+template <class S> static int sparse_occupancy(int kernel, int lanes, int window_smem, bool peer, int block) {
+    return peer ? sparse_occupancy_t<S, true>(kernel, lanes, window_smem, block) : sparse_occupancy_t<S, false>(kernel, lanes, window_smem, block);
 }
 
 void MatrixImpl::configure_launch() {
-    block = 256;
+    // csr_scalar may run with 128-thread CTAs (EIGSOL_B200_SCALAR_BLOCK=128): work units of 128 rows halve the
+    // quantisation of a small per-rank problem over the persistent grid (8 GPUs on C5: 9.2 units of 256 rows per CTA)
+    block = (!dense && kernel == K_CSR_SCALAR && scalar_block == 128) ? 128 : 256;
     const int64_t s = ss();
     if (dense) {
-        const int RT = block * (dtype ? 1 : 2);
+        const int RT = block * (dtype ? 1 : 2) * (gemv_var == 2 ? 2 : 1);  // rows per CTA (kernels.cuh: GemvRows)
         ntiles = int(std::max<int64_t>((nloc + RT - 1) / RT, 1));
         const int target = sm_count * env_int("EIGSOL_B200_GEMV_WAVES", 4);
         nseg = std::max(1, target / ntiles);
@@ -1362,7 +1367,7 @@ void MatrixImpl::configure_launch() {
         stored_bytes = s * lda * ext_len + s * (ext_len + nloc) + 2 * s * int64_t(nseg) * lda;
     } else {
         const bool peer = xmode == MODE_PEER;
-        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes, window_smem, peer) : sparse_occupancy<double>(kernel, lanes, window_smem, peer);
+        const int occ = dtype ? sparse_occupancy<double2>(kernel, lanes, window_smem, peer, block) : sparse_occupancy<double>(kernel, lanes, window_smem, peer, block);
         const int resident = sm_count * occ;
         int64_t need = 1;
         switch (kernel) {
@@ -1461,7 +1466,10 @@ template <class S, bool PEER> static void launch_sparse_t(MatrixImpl& m, int ph)
     const dim3 g(m.grid), b(B);
     cudaStream_t st = m.stream;
     switch (m.kernel) {
-        case K_CSR_SCALAR: launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B, PEER>, g, b, 0, A, it, ph); break;
+        case K_CSR_SCALAR:
+            if (m.block == 128) launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, 128, PEER>, g, dim3(128), 0, A, it, ph);
+            else launch_pdl(m.pdl, st, spmv_csr_scalar_kernel<S, B, PEER>, g, b, 0, A, it, ph);
+            break;
         case K_CSR_WINDOW:
             launch_pdl(m.pdl, st, spmv_csr_window_kernel<S, B, PEER>, g, b, size_t(m.window_smem), A, m.d_window.as<int2>(), it, ph);
             break;
@@ -1496,12 +1504,15 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>(), m.gemv_map};
     const dim3 g(m.grid), b(B);
+    auto go = [&](auto kern) { launch_pdl(m.pdl, m.stream, kern, g, b, 0, A, it, ph); };
     if (m.xmode == MODE_PEER) {
-        if (m.gemv_var) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 1>, g, b, 0, A, it, ph);
-        else launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, true, 0>, g, b, 0, A, it, ph);
+        if (m.gemv_var == 2) go(gemv_colmajor_kernel<S, B, true, 2>);
+        else if (m.gemv_var == 1) go(gemv_colmajor_kernel<S, B, true, 1>);
+        else go(gemv_colmajor_kernel<S, B, true, 0>);
     } else {
-        if (m.gemv_var) launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 1>, g, b, 0, A, it, ph);
-        else launch_pdl(m.pdl, m.stream, gemv_colmajor_kernel<S, B, false, 0>, g, b, 0, A, it, ph);
+        if (m.gemv_var == 2) go(gemv_colmajor_kernel<S, B, false, 2>);
+        else if (m.gemv_var == 1) go(gemv_colmajor_kernel<S, B, false, 1>);
+        else go(gemv_colmajor_kernel<S, B, false, 0>);
     }
 }
 

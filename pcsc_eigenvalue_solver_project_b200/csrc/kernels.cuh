@@ -78,6 +78,9 @@ __device__ __forceinline__ double2 ld_stream_f64x2(const double* p) {
     asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
     return r;
 }
+__device__ __forceinline__ void ld_stream_f64x4(const double* p, double (&o)[4]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p));
+}
 __device__ __forceinline__ double ld_stream_f64(const double* p) {
     double r;
     asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(p));
@@ -1026,6 +1029,7 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 // segment order (deterministic), runs the row epilogue and leaves the tile's sums in the tile's slot.
 // =================================================================================================
 constexpr int kGemvChunk = 512;  // columns of x staged per pass
+template <class S, int VAR> struct GemvRows { static constexpr int value = (Sc<S>::is_complex ? 1 : 2) * (VAR == 2 ? 2 : 1); };
 
 // VAR 0: x staged 512 columns at a time, 8 column loads in flight per thread.  VAR 1: 64 columns, 4 loads in flight
 // (fewer registers).  A.tile_major selects which neighbours a CTA has in the launch order: 0 = the column segments of
@@ -1038,9 +1042,9 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
         control_cta<S, BLOCK>(it, true);
         return;
     }
-    constexpr int R = Sc<S>::is_complex ? 1 : 2;
+    constexpr int R = GemvRows<S, VAR>::value;  // rows per thread: 16 bytes (VAR 0, 1) or 32 bytes (VAR 2) per column
     constexpr int RT = BLOCK * R;
-    constexpr int CHUNK = VAR == 0 ? kGemvChunk : 64;
+    constexpr int CHUNK = VAR == 0 ? kGemvChunk : (VAR == 1 ? 64 : 128);
     constexpr int UNROLL = VAR == 0 ? 8 : 4;
     __shared__ __align__(16) S xs[CHUNK];
     __shared__ int s_tile_last;
@@ -1069,7 +1073,18 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
             const S* col = A.a + int64_t(cb) * A.lda + r;
 #pragma unroll UNROLL
             for (int j = 0; j < nc; ++j) {
-                if constexpr (R == 2) {
+                if constexpr (R * sizeof(S) == 32) {
+                    // one 256-bit load per column (SASS LDG.E.ENL2.256): 4 real or 2 complex rows
+                    double a[4];
+                    ld_stream_f64x4(reinterpret_cast<const double*>(col), a);
+                    if constexpr (Sc<S>::is_complex) {
+                        Sc<S>::mac(acc[0], make_double2(a[0], a[1]), xs[j]);
+                        Sc<S>::mac(acc[1], make_double2(a[2], a[3]), xs[j]);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) acc[k] = fma(a[k], xs[j], acc[k]);
+                    }
+                } else if constexpr (R == 2) {
                     const double2 a = ld_stream_f64x2(reinterpret_cast<const double*>(col));
                     acc[0] = fma(a.x, xs[j], acc[0]);
                     acc[1] = fma(a.y, xs[j], acc[1]);

@@ -242,6 +242,25 @@ def test_dense_sizes(orc, n, cplx):
     dm.close()
 
 
+@pytest.mark.parametrize("var", [0, 1, 2])
+@pytest.mark.parametrize("tile_major", [0, 1])
+@pytest.mark.parametrize("cplx", [False, True])
+def test_dense_kernel_variants(orc, monkeypatch, var, tile_major, cplx):
+    """Every streaming-loop variant of the dense kernel (16- / 32-byte loads per column, x staged 512 / 64 / 128
+    columns at a time) and both CTA orders, on sizes that leave ragged row tiles and column segments."""
+    monkeypatch.setenv("EIGSOL_B200_GEMV_VAR", str(var))
+    monkeypatch.setenv("EIGSOL_B200_GEMV_MAP", str(tile_major))
+    for n in (3, 130, 1100, 2051):
+        a = gen.dense_random_hermitian(n, seed=n) if cplx else gen.dense_random_symmetric(n, seed=n)
+        a = a + (0.1j if cplx else 0.1) * np.triu(np.ones((n, n)), 1)   # not symmetric: layout mistakes show
+        x0 = orc.random_unit(n, a.dtype, seed=4)
+        dm = es.DeviceMatrix.from_matrix(es.Matrix(a))
+        y = dm.matvec(x0)
+        assert np.max(np.abs(y - a @ x0)) <= 1e-12 * np.max(np.abs(a @ x0))
+        check_result(dm.power(x0, es.SolverOptions(15, -1.0)), orc.power_dense(a, x0, 15, -1.0))
+        dm.close()
+
+
 def test_dense_nonsymmetric_colmajor_layout(orc):
     # a non-symmetric matrix catches any row/column-major mix-up; also the row-major vector constructor
     n = 37
