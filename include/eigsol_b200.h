@@ -319,7 +319,12 @@ EIGSOL_B200_API int eigsol_b200_halo_plan(int64_t row_count, const int32_t* rowp
                                           int rank, int64_t* halo_count, int32_t* halo_cols,
                                           int64_t* peer_count);
 
-/* Kernel choice from row-length statistics alone (what KERNEL_AUTO does). */
+/* Kernel choice (what KERNEL_AUTO does) from the statistics of a whole CSR matrix with global column indices: row
+ * lengths (mean, max, padding of a sliced layout) and the share of entries on the tridiagonal, which tells PDE stencils
+ * from random-offset bands.  colidx == NULL: row lengths only (the matrix is taken to be stencil-like). */
+EIGSOL_B200_API int eigsol_b200_choose_kernel_csr(int dtype, int64_t rows, const int32_t* rowptr,
+                                                  const int32_t* colidx, int* kernel_out, int* lanes_out);
+/* The same from row lengths alone (= colidx NULL). */
 EIGSOL_B200_API int eigsol_b200_choose_kernel(int dtype, int64_t rows, const int32_t* rowptr,
                                               int* kernel_out, int* lanes_out);
 

@@ -33,7 +33,7 @@ EXPORTS = [
     "eigsol_b200_comm_unique_id", "eigsol_b200_comm_create", "eigsol_b200_comm_destroy",
     "eigsol_b200_comm_max_float",
     "eigsol_b200_csc_to_csr", "eigsol_b200_partition_rows", "eigsol_b200_halo_plan",
-    "eigsol_b200_choose_kernel", "eigsol_b200_random_unit",
+    "eigsol_b200_choose_kernel", "eigsol_b200_choose_kernel_csr", "eigsol_b200_random_unit",
 ]
 
 
@@ -121,6 +121,7 @@ def lib():
         "eigsol_b200_partition_rows": (i, [i64, i32p, i, i64p]),
         "eigsol_b200_halo_plan": (i, [i64, i32p, i32p, i, i64p, i, i64p, i32p, i64p]),
         "eigsol_b200_choose_kernel": (i, [i, i64, i32p, ip, ip]),
+        "eigsol_b200_choose_kernel_csr": (i, [i, i64, i32p, i32p, ip, ip]),
         "eigsol_b200_random_unit": (i, [i, i64, i, vp]),
     }
     for name, (res, args) in sig.items():

@@ -294,6 +294,7 @@ struct MatrixImpl {
     void compute_prescale();
     void init_sparse_device_rows(const int32_t* rowptr, const int32_t* colidx, const void* values);
     void finish_rows_on_device();
+    double near_diag_on_device(int64_t row0);
     void init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner, const void* values);
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
     void plan_exchange();
@@ -618,6 +619,7 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     Trace tr;
     csr = std::move(a);
     local_nnz = csr.nnz();
+    const double near_diag = row_stats(nloc, csr.rowptr.data(), csr.colidx.data(), lo).near_diag;  // global columns still
     halo = halo_plan(nloc, csr.rowptr.data(), csr.colidx.data(), row_begin, rank);
     nhalo = int64_t(halo.cols.size());
     tr.mark("rows: halo plan");
@@ -630,6 +632,7 @@ void MatrixImpl::init_sparse_local(CsrHost&& a) {
     setup_peer();
     tr.mark("rows: exchange plan + peer map");
     stats = row_stats(nloc, csr.rowptr.data());
+    stats.near_diag = near_diag;
     tr.mark("rows: row stats");
     if (nranks > 1) {
         const std::vector<int64_t> all = comm_allgather_i64(comm, local_nnz);
@@ -774,6 +777,7 @@ void MatrixImpl::init_sparse_device_csc(int64_t rows, int64_t cols, const int32_
         stats.min = hf[2];
         stats.cv = stats.mean > 0 ? std::sqrt(var / double(rows)) / stats.mean : 0.0;
         stats.sell_fill = double(padded) / double(nnz);
+        stats.near_diag = near_diag_on_device(0);
     } else {
         alloc_vectors();
         plan_exchange();
@@ -1001,6 +1005,20 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     finish_rows_on_device();
 }
 
+// Fraction of the resident CSR entries (GLOBAL columns) on the tridiagonal: the stencil statistic of the kernel choice.
+double MatrixImpl::near_diag_on_device(int64_t row0) {
+    if (local_nnz == 0 || nloc == 0) return 1.0;
+    DevBuf d_cnt;
+    d_cnt.alloc_pooled(sizeof(unsigned long long), stream, true, 0);
+    const int g = int(std::max<int64_t>(1, std::min<int64_t>((nloc + 255) / 256, int64_t(sm_count) * 8)));
+    near_diag_kernel<<<g, 256, 0, stream>>>(d_rowptr.as<int32_t>(), d_colidx.as<int32_t>(), nloc, row0, d_cnt.as<unsigned long long>());
+    ++launches;
+    unsigned long long c = 0;
+    EIGSOL_CUDA(cudaMemcpyAsync(&c, d_cnt.p, sizeof c, cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    return double(c) / double(local_nnz);
+}
+
 // The rank's rows are resident as CSR with GLOBAL columns (d_rowptr / d_colidx / d_vals, local_nnz set): halo
 // discovery, column renumbering, row statistics, exchange plan, kernel choice -- all on the device.
 void MatrixImpl::finish_rows_on_device() {
@@ -1050,6 +1068,7 @@ void MatrixImpl::finish_rows_on_device() {
         nhalo = 0;
     }
     tr.mark("rows(dev): halo discovery");
+    const double near_diag = near_diag_on_device(lo);  // needs the GLOBAL columns: before the renumbering below
     alloc_vectors();
     if (ext_len > INT32_MAX) throw PlanError("local vector length exceeds int32 indices");
     if (nnz > 0) {
@@ -1083,6 +1102,7 @@ void MatrixImpl::finish_rows_on_device() {
         stats.min = hf[2];
         stats.cv = stats.mean > 0 ? std::sqrt(var / double(nloc)) / stats.mean : 0.0;
         stats.sell_fill = double(padded) / double(nnz);
+        stats.near_diag = near_diag;
     }
     EIGSOL_CUDA(cudaGetLastError());
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
@@ -2693,6 +2713,18 @@ int eigsol_b200_halo_plan(int64_t row_count, const int32_t* rowptr, const int32_
         *halo_count = int64_t(h.cols.size());
         if (halo_cols) std::copy(h.cols.begin(), h.cols.end(), halo_cols);
         if (peer_count) std::copy(h.peer_count.begin(), h.peer_count.end(), peer_count);
+        return int(EIGSOL_B200_OK);
+    });
+}
+
+int eigsol_b200_choose_kernel_csr(int dtype, int64_t rows, const int32_t* rowptr, const int32_t* colidx, int* kernel_out,
+                                  int* lanes_out) {
+    if (int e = check_dtype(dtype)) return e;
+    return guarded([&] {
+        if (rows < 0 || !rowptr || !kernel_out || !lanes_out) throw PlanError("null array / negative size");
+        const KernelChoice c = choose_kernel(dtype, row_stats(rows, rowptr, colidx, 0));
+        *kernel_out = c.kernel;
+        *lanes_out = c.lanes;
         return int(EIGSOL_B200_OK);
     });
 }

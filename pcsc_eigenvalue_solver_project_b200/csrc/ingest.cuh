@@ -332,6 +332,23 @@ __global__ void rebase_kernel(int32_t* __restrict__ rowptr, int64_t count, int32
     if (i < count) rowptr[i] -= base;
 }
 
+// entries with |column - row| <= 1 (GLOBAL column indices; row0 = global index of the block's first row): the
+// "tridiagonal core" statistic of the kernel choice (plan.hpp).  One thread per row.
+__global__ void near_diag_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int64_t rows,
+                                 int64_t row0, unsigned long long* count) {
+    unsigned long long c = 0;
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < rows; i += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t g = row0 + i;
+        for (int32_t p = rowptr[i]; p < rowptr[i + 1]; ++p) {
+            const int64_t d = int64_t(colidx[p]) - g;
+            c += (d >= -1 && d <= 1) ? 1ull : 0ull;
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) c += __shfl_down_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
+
 // ---- row-block ingest (multi-GPU: each rank holds rows [lo, hi) in CSR with GLOBAL columns) ----------
 // mark[c] = 1 for every referenced column outside [lo, hi); bit 1 of flags = column out of range
 __global__ void rows_mark_kernel(const int32_t* __restrict__ colidx, int64_t nnz, int64_t n, int64_t lo, int64_t hi,

@@ -114,9 +114,12 @@ struct RowStats {
     int64_t rows = 0, nnz = 0;
     double mean = 0, max = 0, min = 0, cv = 0;
     double sell_fill = 1.0;  // padded entries / nnz for a 64-row slice (1.0 = no padding)
+    double near_diag = 1.0;  // fraction of the entries with |column - row| <= 1 (the tridiagonal core every PDE stencil
+                             // has); 1.0 when the column indices were not looked at
 };
 
-inline RowStats row_stats(int64_t rows, const int32_t* rowptr) {
+// colidx (optional): GLOBAL column indices of the rows, row0 = global index of the first row
+inline RowStats row_stats(int64_t rows, const int32_t* rowptr, const int32_t* colidx = nullptr, int64_t row0 = 0) {
     RowStats s;
     s.rows = rows;
     if (rows == 0) return s;
@@ -142,6 +145,15 @@ inline RowStats row_stats(int64_t rows, const int32_t* rowptr) {
     s.min = mn;
     s.cv = s.mean > 0 ? std::sqrt(var / double(rows)) / s.mean : 0.0;
     s.sell_fill = s.nnz > 0 ? double(padded) / double(s.nnz) : 1.0;
+    if (colidx && s.nnz > 0) {
+        int64_t near = 0;
+        for (int64_t i = 0; i < rows; ++i)
+            for (int32_t p = rowptr[i]; p < rowptr[i + 1]; ++p) {
+                const int64_t d = int64_t(colidx[p]) - (row0 + i);
+                near += (d >= -1 && d <= 1) ? 1 : 0;
+            }
+        s.near_diag = double(near) / double(s.nnz);
+    }
     return s;
 }
 
@@ -153,11 +165,15 @@ struct KernelChoice {
     int lanes = 0;  // CSR_VECTOR: lanes per row; SELL: rows per lane
 };
 
-// The dispatch rule (DESIGN.md "kernel choice"; thresholds from profiles/r01_variants*.jsonl, B200):
-//   very short rows, no long outliers   -> CSR_SCALAR: thread per row straight off the CSR arrays
-//                                          (2D/3D stencils: 98 % of the measured copy bandwidth)
-//   short / medium rows, padding <= 2.5x -> SELL (R = 2 rows per lane for f64, 1 for c128): every
-//                                          stream coalesced; wins from ~8 to 64 entries per row
+// The dispatch rule (DESIGN.md "kernel choice"; every threshold is backed by a measured sweep on the B200,
+// profiles/r02/variants_*.jsonl, and pinned by tests/test_host_plan.py::test_dispatch_rule_picks_the_measured_winner):
+//   very short rows, no long outliers, AND
+//     stencil-like (>= 25 % of the entries on the tridiagonal: 2D/3D Laplacians, 43-60 %)  -> CSR_SCALAR: the gathers of a
+//         warp fall into a handful of lines, thread-per-row off the CSR arrays runs at 98 % of the copy bandwidth and
+//         beats SELL by 7-15 %
+//     or irregular enough that SELL would pad heavily (fill > 2.25, e.g. Poisson(4) rows)    -> CSR_SCALAR
+//   short / medium rows, padding <= 2.5x -> SELL (R = 2 rows per lane for f64, 1 for c128): every stream coalesced;
+//         wins from 4 regular entries per row up to 64 (random-offset bands: 8 % at 4, 46 % at 8, 20-60 % at 12..64)
 //   short rows with long outliers        -> CSR_STREAM (long rows reduced by a whole CTA)
 //   long rows                            -> CSR_VECTOR, lanes = pow2 <= mean clipped to [2, 32]
 inline KernelChoice choose_kernel(int dtype, const RowStats& s) {
@@ -166,7 +182,7 @@ inline KernelChoice choose_kernel(int dtype, const RowStats& s) {
         c.kernel = K_CSR_SCALAR;
         return c;
     }
-    if (s.mean <= 8.0 && s.max <= 32.0) {
+    if (s.mean <= 8.0 && s.max <= 32.0 && (s.near_diag >= 0.25 || s.sell_fill > 2.25)) {
         c.kernel = K_CSR_SCALAR;
         return c;
     }

@@ -213,3 +213,49 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h", ".cpp")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "libeigsol_oracle" not in text and "oracle/" not in text.replace("oracle/ ", ""), f
+
+
+# ---- the dispatch rule against the measured sweeps (profiles/r02/variants_*.jsonl, B200) ----------------------------
+def _measured_variants():
+    import glob
+    import json
+    rows = []
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r02", "variants_*.jsonl"))):
+        for line in open(f):
+            if line.startswith("{"):
+                rows.append(json.loads(line))
+    by = {}
+    for r in rows:
+        by.setdefault(r["cfg"], {})[(r["kernel"], r["lanes"])] = min(r["ms_per_trip"], by.get(r["cfg"], {}).get((r["kernel"], r["lanes"]), 1e9))
+    return by
+
+
+@pytest.mark.parametrize("cfg", ["s4", "s8", "s12", "s16", "s32", "s64", "i4", "i8", "i12", "i16", "i32", "s16c", "i8c", "i32c"])
+def test_dispatch_rule_picks_the_measured_winner(cfg):
+    """choose_kernel on the very matrices tools/variant_bench.py timed on the B200 (2^20 rows, band 4096; s<k> regular
+    k-entry rows, i<k> Poisson(k) rows, trailing c = complex): the variant it picks must be the measured winner or
+    within 5 % of it."""
+    by = _measured_variants()
+    if cfg not in by:
+        pytest.skip(f"no measured sweep for {cfg} under profiles/r02")
+    cplx = cfg.endswith("c")
+    k = int(cfg[1:].rstrip("c"))
+    rp, ci, _ = gen.banded_random_csr(1 << 20, k, 4096, seed=1, regular=cfg[0] == "s")
+    kern, lanes = C.c_int(0), C.c_int(0)
+    _capi.check(_capi.lib().eigsol_b200_choose_kernel_csr(1 if cplx else 0, rp.size - 1, _capi.ptr(rp), _capi.ptr(ci),
+                                                          C.byref(kern), C.byref(lanes)))
+    name = _capi.KERNEL_NAMES[kern.value]
+    picked = by[cfg].get((name, lanes.value if name in ("sell", "csr_vector") else 0))
+    assert picked is not None, (name, lanes.value, sorted(by[cfg]))
+    best = min(by[cfg].values())
+    assert picked <= 1.05 * best, (cfg, name, lanes.value, picked, best)
+
+
+def test_dispatch_rule_keeps_the_stencils_on_thread_per_row():
+    """The BASELINE configs: 2D / 3D Laplacians (43-60 % of the entries on the tridiagonal) stay on csr_scalar, which the
+    round-1 sweeps measured 7-15 % ahead of SELL on them (profiles/r01_notes.md)."""
+    for rp, ci in [gen.laplacian_2d(96)[:2], gen.laplacian_3d(20)[:2], gen.hermitian_laplacian_2d(64, 3, False)[:2]]:
+        kern, lanes = C.c_int(0), C.c_int(0)
+        _capi.check(_capi.lib().eigsol_b200_choose_kernel_csr(0, rp.size - 1, _capi.ptr(rp), _capi.ptr(ci), C.byref(kern),
+                                                              C.byref(lanes)))
+        assert kern.value == _capi.KERNEL_CSR_SCALAR
