@@ -88,6 +88,7 @@ struct Comm {
     ncclComm_t nccl_comm = nullptr;
     LocalGroup* local = nullptr;
     std::vector<int> local_devices;  // single-process group: CUDA device of every rank
+    bool pool_shared = false;        // ... and this device's memory pool is readable / writable by every peer of the group
     cudaStream_t stream = nullptr;
     DevBuf scratch;  // small device scratch for setup-time collectives
     ~Comm() {
@@ -379,10 +380,10 @@ void MatrixImpl::alloc_vectors() {
     // (CUDA IPC / peer access), which needs plain allocations
     for (auto& b : buf) {
         if (b.p && b.bytes == size_t(ext_len) * ss()) continue;  // buf[0] may be in place already (preloaded x0)
-        if (nranks == 1) b.alloc_pooled(size_t(ext_len) * ss(), stream, true, 256);
+        if (nranks == 1 || (comm && comm->pool_shared)) b.alloc_pooled(size_t(ext_len) * ss(), stream, true, 256);
         else b.alloc(size_t(ext_len) * ss(), 256);
     }
-    if (nranks == 1) d_xloc.alloc_pooled(size_t(std::max<int64_t>(nloc, 1)) * ss(), stream);
+    if (nranks == 1 || (comm && comm->pool_shared)) d_xloc.alloc_pooled(size_t(std::max<int64_t>(nloc, 1)) * ss(), stream);
     else d_xloc.alloc(size_t(std::max<int64_t>(nloc, 1)) * ss());
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
     if (nranks > 1 && !(comm && comm->local)) d_xglob.alloc(size_t(std::max<int64_t>(n, 1)) * ss());  // NCCL gather target
@@ -821,11 +822,18 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
     const size_t s = size_t(ss());
     const int B = 256;
     DevBuf d_souter, d_sinner, d_svals, d_scol, d_flags;
+    const bool pooled = comm->pool_shared;  // peers read the slabs: pool memory only if the pool is shared with them
+    auto get = [&](DevBuf& b, size_t bytes, bool zero) {
+        if (pooled) b.alloc_pooled(bytes, stream, zero);
+        else if (zero) b.alloc(bytes);
+        else b.alloc_raw(bytes);
+    };
     d_flags.alloc(64);
-    d_souter.alloc(sizeof(int32_t) * size_t(scols + 1));
-    d_sinner.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(snnz, 1)));
-    d_scol.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(snnz, 1)));
-    d_svals.alloc(size_t(std::max<int64_t>(snnz, 1)) * s);
+    get(d_souter, sizeof(int32_t) * size_t(scols + 1), false);
+    get(d_sinner, sizeof(int32_t) * size_t(std::max<int64_t>(snnz, 1)), false);
+    get(d_scol, sizeof(int32_t) * size_t(std::max<int64_t>(snnz, 1)), false);
+    get(d_svals, size_t(std::max<int64_t>(snnz, 1)) * s, false);
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));  // the uploader threads write from their own streams
     {
         StagedUploader up;
         up.add(d_souter.p, outer + c0, sizeof(int32_t) * size_t(scols + 1));
@@ -883,20 +891,20 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
     // 2. pull them, slab by slab, into COO arrays (key = local row, global column, value)
     const size_t nz = size_t(std::max<int64_t>(nnz, 1));
     DevBuf d_key, d_col, d_val, d_iota, d_sel, d_nsel, d_tmp;
-    d_key.alloc(sizeof(int32_t) * nz);
-    d_col.alloc(sizeof(int32_t) * nz);
-    d_val.alloc(nz * s);
-    d_iota.alloc(sizeof(int32_t) * nz);
-    d_sel.alloc(sizeof(int32_t) * size_t(max_snnz));
+    get(d_key, sizeof(int32_t) * nz, false);
+    get(d_col, sizeof(int32_t) * nz, false);
+    get(d_val, nz * s, false);
+    get(d_iota, sizeof(int32_t) * nz, false);
+    get(d_sel, sizeof(int32_t) * size_t(max_snnz), false);
     d_nsel.alloc(sizeof(int));
-    d_rowptr.alloc(sizeof(int32_t) * size_t(nloc + 1));  // zero-filled: the row histogram
+    get(d_rowptr, sizeof(int32_t) * size_t(nloc + 1), true);  // zero-filled: the row histogram
     size_t tb = 0;
     {
         cub::CountingInputIterator<int32_t> it0(0);
         EIGSOL_CUDA(cub::DeviceSelect::If(nullptr, tb, it0, d_sel.as<int32_t>(), d_nsel.as<int>(), int(max_snnz),
                                           RowInRange{nullptr, 0, 0}, stream));
     }
-    d_tmp.alloc(tb);
+    get(d_tmp, tb, false);
     int64_t off = 0;
     for (int q = 0; q < nranks; ++q) {
         const int64_t nq = int64_t(cnt[size_t(q)]);
@@ -932,22 +940,22 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
     d_sel.release();
     tr.mark("group csc: pull");
     // 3. COO (column-major order) -> CSR: stable sort by local row keeps the columns ascending inside a row
-    d_colidx.alloc(sizeof(int32_t) * nz);
-    d_vals.alloc(nz * s);
+    get(d_colidx, sizeof(int32_t) * nz, false);
+    get(d_vals, nz * s, false);
     if (nnz > 0) {
         DevBuf d_perm, d_keys2, d_t1, d_t2;
-        d_perm.alloc(sizeof(int32_t) * nz);
-        d_keys2.alloc(sizeof(int32_t) * nz);
+        get(d_perm, sizeof(int32_t) * nz, false);
+        get(d_keys2, sizeof(int32_t) * nz, false);
         int end_bit = 1;
         while (end_bit < 31 && (int64_t(1) << end_bit) < std::max<int64_t>(nloc, 2)) ++end_bit;
         size_t t1 = 0, t2 = 0;
         EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, t1, d_key.as<int32_t>(), d_keys2.as<int32_t>(), d_iota.as<int32_t>(),
                                                     d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
-        d_t1.alloc(t1);
+        get(d_t1, t1, false);
         EIGSOL_CUDA(cub::DeviceRadixSort::SortPairs(d_t1.p, t1, d_key.as<int32_t>(), d_keys2.as<int32_t>(), d_iota.as<int32_t>(),
                                                     d_perm.as<int32_t>(), int(nnz), 0, end_bit, stream));
         EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, t2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(nloc + 1), stream));
-        d_t2.alloc(t2);
+        get(d_t2, t2, false);
         EIGSOL_CUDA(cub::DeviceScan::ExclusiveSum(d_t2.p, t2, d_rowptr.as<int32_t>(), d_rowptr.as<int32_t>(), int(nloc + 1), stream));
         const unsigned gnz = unsigned((nnz + B - 1) / B);
         if (dtype)
@@ -1953,6 +1961,26 @@ struct LocalSolver {
             c->local = &group;
             c->local_devices = devices;
             EIGSOL_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+            {
+                // let the peers of the group read and write this device's stream-ordered pool: slabs, ring buffers and
+                // temporaries of a group can then come from the pool like those of a single GPU
+                cudaMemPool_t pool = nullptr;
+                bool ok = cudaDeviceGetDefaultMemPool(&pool, c->device) == cudaSuccess && pool;
+                for (int q = 0; q < P && ok; ++q) {
+                    if (q == r) continue;
+                    int can = 0;
+                    ok = cudaDeviceCanAccessPeer(&can, devices[size_t(q)], c->device) == cudaSuccess && can;
+                    if (!ok) break;
+                    cudaMemAccessDesc d;
+                    std::memset(&d, 0, sizeof d);
+                    d.location.type = cudaMemLocationTypeDevice;
+                    d.location.id = devices[size_t(q)];
+                    d.flags = cudaMemAccessFlagsProtReadWrite;
+                    ok = cudaMemPoolSetAccess(pool, &d, 1) == cudaSuccess;
+                }
+                cudaGetLastError();
+                c->pool_shared = ok && env_int("EIGSOL_B200_GROUP_POOL", 1) != 0;
+            }
             comms[size_t(r)] = std::move(c);
             ranks[size_t(r)].reset(new MatrixImpl);
         });

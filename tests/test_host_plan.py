@@ -230,7 +230,7 @@ def _measured_variants():
     return by
 
 
-@pytest.mark.parametrize("cfg", ["s4", "s8", "s12", "s16", "s32", "s64", "i4", "i8", "i12", "i16", "i32", "s16c", "i8c", "i32c"])
+@pytest.mark.parametrize("cfg", ["s4", "s5", "s6", "s7", "s8", "s9", "s10", "s12", "s16", "s32", "s64", "i4", "i8", "i12", "i16", "i32", "s16c", "i8c", "i32c"])
 def test_dispatch_rule_picks_the_measured_winner(cfg):
     """choose_kernel on the very matrices tools/variant_bench.py timed on the B200 (2^20 rows, band 4096; s<k> regular
     k-entry rows, i<k> Poisson(k) rows, trailing c = complex): the variant it picks must be the measured winner or

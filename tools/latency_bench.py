@@ -35,7 +35,7 @@ def main():
             name, _, kv = item.partition(":")
             configs.append((name, dict(p.split("=") for p in kv.split(",") if p)))
     for cfg_name, cfg_env in configs:
-      for k in [k for k in os.environ if k.startswith("EIGSOL_B200_") and k not in ("EIGSOL_B200_EXCHANGE",)]:
+      for k in [k for k in os.environ if k.startswith("EIGSOL_B200_") and k not in ("EIGSOL_B200_EXCHANGE", "EIGSOL_B200_PEER_STATS")]:
           del os.environ[k]
       os.environ.update(cfg_env)
       for g in grids:

@@ -14,9 +14,9 @@ g = int(os.environ.get("GRID", 256))
 n = g ** 3
 rp, ci, v = gen.laplacian_3d(g)
 outer, inner, vals = gen.csr_to_csc_hermitian(rp, ci, v)
-M = es.Matrix(((n, n), outer, inner, vals))
 x0 = es.random_unit(n, np.float64, seed=1)
 for rep in range(3):
+    M = es.Matrix(((n, n), outer, inner, vals))  # a fresh Matrix per call: every call uploads (a Matrix keeps its device copy)
     t0 = time.perf_counter()
     r = es.powerMethod(M, es.SolverOptions(20, -1.0), x0=x0)
     dt = time.perf_counter() - t0
