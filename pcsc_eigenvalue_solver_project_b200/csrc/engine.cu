@@ -176,7 +176,7 @@ static std::vector<char> comm_allgather_bytes(Comm* c, const void* mine, size_t 
         return out;
     }
     DevBuf d;
-    d.alloc(out.size());
+    d.alloc_plain(out.size());  // NCCL buffer
     EIGSOL_CUDA(cudaMemcpyAsync(d.as<char>() + bytes * c->rank, mine, bytes, cudaMemcpyHostToDevice, c->stream));
     EIGSOL_NCCL(nccl().GroupStart());
     for (int r = 0; r < c->nranks; ++r)
@@ -273,6 +273,7 @@ struct MatrixImpl {
     bool begun = false;
     int max_trips = 0;
     const void* preload_x0 = nullptr;  // one-shot call: host start vector to upload together with the matrix
+    DevBuf d_x0pre;                    // group rank: this rank's rows of the preloaded start vector (copied into buf[0] by begin)
     bool x0_preloaded = false;         // ... and it is in buf[0] already (consumed by the next begin() with that pointer)
     cudaGraphExec_t graph = nullptr, graph_short = nullptr;  // graph_len launches / kRing launches
     int graph_len = 0;
@@ -364,7 +365,8 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     EIGSOL_CUDA(cudaEventCreate(&ev0));
     EIGSOL_CUDA(cudaEventCreate(&ev1));
     d_state.alloc(sizeof(PowerState));
-    d_scal.alloc(kRing * 4 * sizeof(double));
+    if (comm && comm->nccl_comm) d_scal.alloc_plain(kRing * 4 * sizeof(double));  // NCCL buffer (split mode, begin barrier)
+    else d_scal.alloc(kRing * 4 * sizeof(double));
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
     scalar_block = env_int("EIGSOL_B200_SCALAR_BLOCK", 256) == 128 ? 128 : 256;
@@ -381,12 +383,12 @@ void MatrixImpl::alloc_vectors() {
     for (auto& b : buf) {
         if (b.p && b.bytes == size_t(ext_len) * ss()) continue;  // buf[0] may be in place already (preloaded x0)
         if (nranks == 1 || (comm && comm->pool_shared)) b.alloc_pooled(size_t(ext_len) * ss(), stream, true, 256);
-        else b.alloc(size_t(ext_len) * ss(), 256);
+        else b.alloc_plain(size_t(ext_len) * ss(), 256);  // exported with CUDA IPC
     }
     if (nranks == 1 || (comm && comm->pool_shared)) d_xloc.alloc_pooled(size_t(std::max<int64_t>(nloc, 1)) * ss(), stream);
     else d_xloc.alloc(size_t(std::max<int64_t>(nloc, 1)) * ss());
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
-    if (nranks > 1 && !(comm && comm->local)) d_xglob.alloc(size_t(std::max<int64_t>(n, 1)) * ss());  // NCCL gather target
+    if (nranks > 1 && !(comm && comm->local)) d_xglob.alloc_plain(size_t(std::max<int64_t>(n, 1)) * ss());  // NCCL gather target
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -436,9 +438,9 @@ void MatrixImpl::plan_exchange() {
         total_send = send_off[nranks];
 
         DevBuf d_need;  // my halo columns (global), grouped by owner
-        d_need.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(nhalo, 1)));
+        d_need.alloc_plain(sizeof(int32_t) * size_t(std::max<int64_t>(nhalo, 1)));  // NCCL buffer
         d_need.upload(halo.cols.data(), sizeof(int32_t) * size_t(nhalo), c->stream);
-        d_send_idx.alloc(sizeof(int32_t) * size_t(std::max<int64_t>(total_send, 1)));
+        d_send_idx.alloc_plain(sizeof(int32_t) * size_t(std::max<int64_t>(total_send, 1)));  // NCCL buffer
         EIGSOL_NCCL(nccl().GroupStart());
         for (int q = 0; q < nranks; ++q) {
             if (q == rank) continue;
@@ -470,7 +472,7 @@ void MatrixImpl::plan_exchange() {
     }
     if (total_send) {
         EIGSOL_CUDA(cudaMemcpy(d_send_idx.p, idx.data(), sizeof(int32_t) * size_t(total_send), cudaMemcpyHostToDevice));
-        d_sendbuf.alloc(size_t(total_send) * ss());
+        d_sendbuf.alloc_plain(size_t(total_send) * ss());  // NCCL buffer (split mode)
     }
 }
 
@@ -494,8 +496,15 @@ void MatrixImpl::setup_peer() {
     const char* want = std::getenv("EIGSOL_B200_EXCHANGE");
     const bool local = comm->local != nullptr;
     const bool force_nccl = !local && want && std::string(want) == "nccl";
-    d_scal_in.alloc(sizeof(double) * kRing * kMaxPeers * 4);
-    d_flag_in.alloc(sizeof(unsigned long long) * 2 * kMaxPeers);  // [0,8): trip flags, [8,16): gate flags
+    // mailboxes and flags are written by the peers: plain memory (CUDA IPC export / peer access), unless the group
+    // shares this device's pool
+    if (local && comm->pool_shared) {
+        d_scal_in.alloc(sizeof(double) * kRing * kMaxPeers * 4);
+        d_flag_in.alloc(sizeof(unsigned long long) * 2 * kMaxPeers);
+    } else {
+        d_scal_in.alloc_plain(sizeof(double) * kRing * kMaxPeers * 4);
+        d_flag_in.alloc_plain(sizeof(unsigned long long) * 2 * kMaxPeers);  // [0,8): trip flags, [8,16): gate flags
+    }
     PeerBlob mine;
     std::memset(&mine, 0, sizeof mine);
     int ok = (nranks <= kMaxPeers && !force_nccl) ? 1 : 0;
@@ -839,7 +848,14 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
         up.add(d_souter.p, outer + c0, sizeof(int32_t) * size_t(scols + 1));
         up.add(d_sinner.p, inner + e0, sizeof(int32_t) * size_t(snnz));
         up.add(d_svals.p, static_cast<const char*>(values) + size_t(e0) * s, size_t(snnz) * s);
+        if (preload_x0 && nloc > 0) {
+            // one-shot call: this rank's rows of the start vector ride on the slab upload
+            get(d_x0pre, size_t(nloc) * s, false);
+            EIGSOL_CUDA(cudaStreamSynchronize(stream));
+            up.add(d_x0pre.p, static_cast<const char*>(preload_x0) + size_t(lo) * s, size_t(nloc) * s);
+        }
         EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+        x0_preloaded = preload_x0 != nullptr;
     }
     tr.mark("group csc: slab upload");
     if (e0 != 0) rebase_kernel<<<unsigned((scols + 1 + B - 1) / B), B, 0, stream>>>(d_souter.as<int32_t>(), scols + 1, int32_t(e0));
@@ -1578,11 +1594,17 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol, bool unit_scale) 
     issued = 0;
     const size_t s = size_t(ss());
     EIGSOL_CUDA(cudaMemcpyAsync(d_state.p, &st, sizeof st, cudaMemcpyHostToDevice, stream));
-    const bool in_place = x0_preloaded && x0 == preload_x0;  // one-shot call: x0 came up with the matrix
+    bool in_place = x0_preloaded && x0 == preload_x0;  // one-shot call: x0 came up with the matrix
     x0_preloaded = false;
     preload_x0 = nullptr;
+    const bool staged_slice = in_place && d_x0pre.p != nullptr;  // group rank: the rows sit in d_x0pre, not in buf[0] yet
+    if (staged_slice) in_place = false;
     for (int b = in_place ? 1 : 0; b < kRing; ++b) EIGSOL_CUDA(cudaMemsetAsync(buf[b].p, 0, size_t(ext_len) * s, stream));
-    if (nloc && !in_place) {
+    if (staged_slice) {
+        if (nloc) EIGSOL_CUDA(cudaMemcpyAsync(buf[0].p, d_x0pre.p, size_t(nloc) * s, cudaMemcpyDeviceToDevice, stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(stream));
+        d_x0pre.release();
+    } else if (nloc && !in_place) {
         const char* src = static_cast<const char*>(x0) + size_t(lo) * s;
         if (size_t(nloc) * s >= (size_t(32) << 20)) {
             // a large pageable vector: several host threads through pinned staging instead of one synchronous copy
@@ -2182,10 +2204,12 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
             for (int64_t j = 0; j < cols; ++j)
                 if (outer[j + 1] < outer[j]) throw PlanError("CSC outer index not monotone");
             const std::vector<int64_t> rb = partition_rows(cols, outer, h->group->P);
+            const void* pre = g_preload_x0;  // (thread-local of the calling thread: hand it to the rank threads)
             h->each([&](MatrixImpl& m, int r) {
                 m.init_common(dtype, h->group->comms[size_t(r)].get());
                 m.n = rows;
                 m.row_begin = rb;
+                m.preload_x0 = pre;
                 m.init_sparse_group_csc(rows, cols, outer, inner, values);
             });
             *out = h.release();
@@ -2605,7 +2629,7 @@ int eigsol_b200_comm_create(int rank, int nranks, const void* id128, int device,
         c.device = device;
         EIGSOL_CUDA(cudaSetDevice(device));
         EIGSOL_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
-        c.scratch.alloc(sizeof(int64_t) * size_t(4 * nranks + 16));
+        c.scratch.alloc_plain(sizeof(int64_t) * size_t(4 * nranks + 16));  // NCCL buffer
         if (nranks > 1) {
             ncclUniqueId id;
             std::memcpy(&id, id128, sizeof id);

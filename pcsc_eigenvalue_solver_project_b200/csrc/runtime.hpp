@@ -85,7 +85,9 @@ struct DevBuf {
         else if (pad) EIGSOL_CUDA(cudaMemsetAsync(static_cast<char*>(p) + n, 0, pad, st));
     }
     // pad: extra zeroed bytes behind the payload so vector loads may over-read safely
-    void alloc(size_t n, size_t pad = 64) {
+    // Plain cudaMalloc, zero-filled and synchronised: for memory that is exported to other processes (CUDA IPC needs
+    // cudaMalloc memory) or mapped by peers without a shared pool.
+    void alloc_plain(size_t n, size_t pad = 64) {
         release();
         bytes = n;
         EIGSOL_CUDA(cudaMalloc(&p, n + pad));
@@ -93,6 +95,22 @@ struct DevBuf {
         // to non-blocking streams: without this synchronisation the zero fill may land AFTER an upload.
         EIGSOL_CUDA(cudaMemset(p, 0, n + pad));
         EIGSOL_CUDA(cudaDeviceSynchronize());
+    }
+    // The default: zero-filled memory from the device's stream-ordered pool, ready for use on ANY stream when the call
+    // returns (allocation and fill run on the calling thread's own stream, which is then synchronised -- no
+    // device-wide synchronisation, no driver round trip once the pool is warm).
+    void alloc(size_t n, size_t pad = 64) {
+        release();
+        bytes = n;
+        if (cudaMallocAsync(&p, n + pad, cudaStreamPerThread) != cudaSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+            alloc_plain(n, pad);
+            return;
+        }
+        pooled = true;
+        EIGSOL_CUDA(cudaMemsetAsync(p, 0, n + pad, cudaStreamPerThread));
+        EIGSOL_CUDA(cudaStreamSynchronize(cudaStreamPerThread));
     }
     // no zero fill, no synchronisation: for buffers every byte of which is written before it is read
     void alloc_raw(size_t n, size_t pad = 64) {
