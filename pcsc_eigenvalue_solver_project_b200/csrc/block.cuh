@@ -26,6 +26,51 @@ template <class S> struct BlockArgs {
     int chunk;          // SpMM kernels: units are dealt to the CTAs in runs of `chunk` consecutive units
 };
 
+// Multi-GPU wiring of the block iteration (one rank; nullptr on one GPU).  The block is row-sharded like the single
+// vector: every rank holds [own rows | halo rows] x K, the SpMM writes the own rows of the next block, a small push
+// kernel copies the rows the peers reference into THEIR halo segments (NVLink stores), and the control launch --
+// which is a synchronisation point of the iteration anyway -- all-reduces the k x k Gram sums through mailboxes in
+// peer memory (rank-ordered sum: the same bits, hence the same decisions, on every rank) and doubles as the barrier
+// that says "every peer's halo rows of this trip have landed".
+constexpr int kBlockMailStride = 2 * (kBlockElems + kBlockMax * (kBlockMax + 1) / 2);  // doubles per rank and parity
+
+struct BlockPeer {
+    int nranks, rank;
+    double* mail_in;                              // local [2][kMaxPeers][kBlockMailStride]
+    double* peer_mail[kMaxPeers];                 // remote mail_in base of rank q (nullptr for self)
+    unsigned long long* flag_in;                  // local [kMaxPeers]
+    unsigned long long* peer_flag[kMaxPeers];     // remote &flag_in[rank] of rank q
+    long long spin_limit;
+    // halo pushes: rows of the freshly written block that peer ranks read
+    int nsend;
+    int send_start[kMaxPeers], send_count[kMaxPeers];
+    void* send_dst[kMaxPeers][2];                 // peer's halo segment, per block buffer (bytes address)
+    int nlist;
+    int list_off[kMaxPeers], list_count[kMaxPeers];
+    void* list_dst[kMaxPeers][2];
+    const int32_t* send_idx;
+};
+
+// Rows of block buffer `which` (the one the SpMM of this trip just wrote) that peers reference -> their halo segments.
+template <class S, int K>
+__global__ void __launch_bounds__(256) block_halo_push_kernel(const BlockPeer* pp, const S* __restrict__ u, int which) {
+    pdl_prologue();
+    const BlockPeer& p = *pp;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    for (int k = 0; k < p.nsend; ++k) {
+        S* dst = static_cast<S*>(p.send_dst[k][which]);
+        const S* src = u + int64_t(p.send_start[k]) * K;
+        const int64_t cnt = int64_t(p.send_count[k]) * K;
+        for (int64_t i = tid; i < cnt; i += nth) dst[i] = src[i];
+    }
+    for (int k = 0; k < p.nlist; ++k) {
+        S* dst = static_cast<S*>(p.list_dst[k][which]);
+        const int32_t* idx = p.send_idx + p.list_off[k];
+        const int64_t cnt = int64_t(p.list_count[k]) * K;
+        for (int64_t i = tid; i < cnt; i += nth) dst[i] = u[int64_t(idx[i / K]) * K + (i % K)];
+    }
+}
+
 // Block-cyclic unit order: CTA b works on units (g * grid + b) * chunk + j, j = 0..chunk-1, g = 0, 1, ...
 // Consecutive units of a run share their near-diagonal operand rows through L1 (a stencil's +-1 line
 // neighbours), while the CTAs running at the same time stay within grid * chunk units of each other, so the
@@ -718,7 +763,8 @@ __global__ void __launch_bounds__(BLOCK) block_combine_kernel(const S* __restric
 // =================================================================================================
 template <int BLOCK>
 __global__ void __launch_bounds__(BLOCK) block_control_kernel(BlockState* st, const double* __restrict__ partials, int nslots,
-                                                              int k, int is_complex, int begin) {
+                                                              int k, int is_complex, int begin, const BlockPeer* peer,
+                                                              unsigned long long epoch) {
     pdl_prologue();
     __shared__ double tot[2 * (kBlockElems + kBlockMax * (kBlockMax + 1) / 2)];
     __shared__ Cx sC[kBlockElems], sW[kBlockElems], sH[kBlockElems], swork[kBlockElems];
@@ -734,6 +780,40 @@ __global__ void __launch_bounds__(BLOCK) block_control_kernel(BlockState* st, co
         if (lane == 0) tot[i] = s;
     }
     __syncthreads();
+    if (peer) {
+        // all-reduce of this rank's sums over the ranks + barrier (see BlockPeer): thread q talks to rank q
+        const BlockPeer& p = *peer;
+        __shared__ int s_ok;
+        if (threadIdx.x == 0) s_ok = 1;
+        __syncthreads();
+        const int par = int(epoch & 1ull);
+        const int q = threadIdx.x;
+        if (q < p.nranks) {
+            double* box = (q == p.rank ? p.mail_in : p.peer_mail[q]) + (size_t(par) * kMaxPeers + p.rank) * kBlockMailStride;
+            for (int i = 0; i < stride; ++i) box[i] = tot[i];
+            if (q != p.rank) {
+                st_release_sys(p.peer_flag[q], epoch);
+                const long long t0 = clock64();
+                while (ld_acquire_sys(p.flag_in + q) < epoch)
+                    if (clock64() - t0 > p.spin_limit) {
+                        s_ok = 0;
+                        break;
+                    }
+            }
+        }
+        __syncthreads();
+        if (!s_ok) {
+            if (threadIdx.x == 0) st->stop = BSTOP_ERROR;
+            return;
+        }
+        for (int i = threadIdx.x; i < stride; i += BLOCK) {
+            double s = 0.0;
+            for (int r = 0; r < p.nranks; ++r)  // rank order: the same sum, bit for bit, on every rank
+                s += ld_volatile_f64(p.mail_in + (size_t(par) * kMaxPeers + r) * kBlockMailStride + i);
+            tot[i] = s;
+        }
+        __syncthreads();
+    }
     for (int e = threadIdx.x; e < nc; e += BLOCK) {
         const int a = e / k, b = e % k;
         sC[a * kBlockLd + b] = cx(tot[e], is_complex ? tot[ne + e] : 0.0);

@@ -1,5 +1,5 @@
 // block_host.cuh -- host side of the block power iteration (included by engine.cu after MatrixImpl).
-// One GPU; uses the matrix copy already resident behind the handle (CSR arrays or the column-major dense
+// One GPU or a row-sharded group (sparse); uses the matrix copy already resident behind the handle (CSR arrays or the column-major dense
 // matrix) and its own two n x K blocks.  Per trip: one SpMM launch (dense: partial + combine) and the
 // single-CTA control launch; the host reads the 2 KB state every `poll` trips.
 #pragma once
@@ -12,18 +12,127 @@ struct BlockResult {
     float ms = 0.f;  // device time of the iteration loop (without upload, Gram pass and download)
 };
 
+// What a rank shows its peers for one block solve (single-process group: raw pointers; process-per-GPU: CUDA IPC).
+struct BlockPeerBlob {
+    cudaIpcMemHandle_t u[2], mail, flag;
+    void *raw_u[2], *raw_mail, *raw_flag;
+    int64_t halo_base;
+    int64_t peer_off[kMaxPeers + 1];
+};
+
+struct BlockPeerHost {
+    DevBuf d_mail, d_flag, d_peer;
+    std::vector<void*> opened;
+    ~BlockPeerHost() {
+        for (void* q : opened) cudaIpcCloseMemHandle(q);
+    }
+};
+
+// Fills and uploads the BlockPeer of this rank for the two block buffers u0 / u1 (ext x K row-major each).
+static const BlockPeer* block_setup_peer(MatrixImpl& m, void* u0, void* u1, size_t row_bytes, BlockPeerHost& host) {
+    if (m.nranks == 1) return nullptr;
+    if (m.xmode != MODE_PEER) throw PlanError("the multi-GPU block power iteration needs the peer-memory exchange (EIGSOL_B200_EXCHANGE=peer)");
+    const bool local = m.comm->local != nullptr;
+    const bool shared_pool = local && m.comm->pool_shared;
+    if (shared_pool) {
+        host.d_mail.alloc(sizeof(double) * 2 * kMaxPeers * kBlockMailStride);
+        host.d_flag.alloc(sizeof(unsigned long long) * kMaxPeers);
+    } else {
+        host.d_mail.alloc_plain(sizeof(double) * 2 * kMaxPeers * kBlockMailStride);
+        host.d_flag.alloc_plain(sizeof(unsigned long long) * kMaxPeers);
+    }
+    BlockPeerBlob mine;
+    std::memset(&mine, 0, sizeof mine);
+    if (!local) {
+        int ok = 1;
+        ok &= cudaIpcGetMemHandle(&mine.u[0], u0) == cudaSuccess;
+        ok &= cudaIpcGetMemHandle(&mine.u[1], u1) == cudaSuccess;
+        ok &= cudaIpcGetMemHandle(&mine.mail, host.d_mail.p) == cudaSuccess;
+        ok &= cudaIpcGetMemHandle(&mine.flag, host.d_flag.p) == cudaSuccess;
+        cudaGetLastError();
+        if (!comm_min_int(m.comm, ok)) throw DeviceError("powerMethod: device error: cannot export the block buffers to the peer GPUs (CUDA IPC)");
+    }
+    mine.raw_u[0] = u0;
+    mine.raw_u[1] = u1;
+    mine.raw_mail = host.d_mail.p;
+    mine.raw_flag = host.d_flag.p;
+    mine.halo_base = m.nloc_pad;
+    for (int q = 0; q <= m.nranks && q <= kMaxPeers; ++q) mine.peer_off[q] = m.halo.peer_off[size_t(q)];
+    const std::vector<char> all = comm_allgather_bytes(m.comm, &mine, sizeof mine);
+    BlockPeer bp;
+    std::memset(&bp, 0, sizeof bp);
+    bp.nranks = m.nranks;
+    bp.rank = m.rank;
+    bp.mail_in = host.d_mail.as<double>();
+    bp.flag_in = host.d_flag.as<unsigned long long>();
+    bp.spin_limit = m.peer_h.spin_limit;
+    bp.send_idx = m.d_send_idx.as<int32_t>();
+    int mapped = 1;
+    for (int q = 0; q < m.nranks && mapped; ++q) {
+        if (q == m.rank) continue;
+        BlockPeerBlob pb;
+        std::memcpy(&pb, all.data() + sizeof(BlockPeerBlob) * size_t(q), sizeof pb);
+        void *ru[2] = {pb.raw_u[0], pb.raw_u[1]}, *rm = pb.raw_mail, *rf = pb.raw_flag;
+        if (!local) {
+            auto open = [&](void** dst, const cudaIpcMemHandle_t& h) {
+                if (cudaIpcOpenMemHandle(dst, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    mapped = 0;
+                    return;
+                }
+                host.opened.push_back(*dst);
+            };
+            open(&ru[0], pb.u[0]);
+            if (mapped) open(&ru[1], pb.u[1]);
+            if (mapped) open(&rm, pb.mail);
+            if (mapped) open(&rf, pb.flag);
+            if (!mapped) break;
+        }
+        bp.peer_mail[q] = static_cast<double*>(rm);
+        bp.peer_flag[q] = static_cast<unsigned long long*>(rf) + m.rank;
+        if (m.send_count[size_t(q)] == 0) continue;
+        const size_t dst_off = size_t(pb.halo_base + pb.peer_off[m.rank]) * row_bytes;
+        if (m.send_contig[size_t(q)]) {
+            const int k = bp.nsend++;
+            bp.send_start[k] = int(m.send_start[size_t(q)]);
+            bp.send_count[k] = int(m.send_count[size_t(q)]);
+            for (int b = 0; b < 2; ++b) bp.send_dst[k][b] = static_cast<char*>(ru[b]) + dst_off;
+        } else {
+            const int k = bp.nlist++;
+            bp.list_off[k] = int(m.send_off[size_t(q)]);
+            bp.list_count[k] = int(m.send_count[size_t(q)]);
+            for (int b = 0; b < 2; ++b) bp.list_dst[k][b] = static_cast<char*>(ru[b]) + dst_off;
+        }
+    }
+    if (!comm_min_int(m.comm, mapped)) throw DeviceError("powerMethod: device error: cannot map the peers' block buffers");
+    host.d_peer.alloc(sizeof(BlockPeer));
+    EIGSOL_CUDA(cudaMemcpy(host.d_peer.p, &bp, sizeof bp, cudaMemcpyHostToDevice));
+    return host.d_peer.as<BlockPeer>();
+}
+
 template <class S, int K>
 static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, double tol, void* x_out, double* lambda_out,
                         BlockResult& res) {
     constexpr int B = 256;
-    const int64_t n = m.n;
+    const int64_t nglob = m.n;
+    // a rank of a group holds [own rows | pad | halo rows]: n = own rows (what the kernels loop over), ext = rows of
+    // the block buffers (what the gathers may address)
+    const bool multi = m.nranks > 1;
+    const int64_t n = multi ? m.nloc : m.n;
+    const int64_t ext = multi ? m.ext_len : m.n;
     const size_t s = sizeof(S);
     cudaStream_t st = m.stream;
     DevBuf u[2], d_xcol, d_state, d_partials, d_dpart;
-    u[0].alloc(size_t(n) * K * s);
-    u[1].alloc(size_t(n) * K * s);
-    d_xcol.alloc(size_t(n) * K * s);
+    const bool plain = multi && !(m.comm->local && m.comm->pool_shared);  // exported with CUDA IPC / mapped by peers
+    for (auto& b : u) {
+        if (plain) b.alloc_plain(size_t(ext) * K * s);
+        else b.alloc(size_t(ext) * K * s);
+    }
+    d_xcol.alloc(size_t(ext) * K * s);
     d_state.alloc(sizeof(BlockState));
+    BlockPeerHost peer_host;
+    const BlockPeer* peer = block_setup_peer(m, u[0].p, u[1].p, size_t(K) * s, peer_host);
+    unsigned long long epoch = 0;
     PinnedBuf h_state;
     h_state.alloc(sizeof(BlockState));
 
@@ -99,10 +208,25 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
     ba.nslots = grid;
     ba.chunk = std::max(1, env_int("EIGSOL_B200_BLOCK_CHUNK", 1));
 
-    // start block: column-major n x K from the caller -> row-major U_0, W_0 = U_0^H U_0, T_0
-    EIGSOL_CUDA(cudaMemcpyAsync(d_xcol.p, x0, size_t(n) * K * s, cudaMemcpyHostToDevice, st));
-    const int gn = int((n + B - 1) / B);
-    block_pack_kernel<S, K><<<gn, B, 0, st>>>(d_xcol.as<S>(), n, ba.u[0]);
+    // start block: column-major nglob x K from the caller -> row-major U_0 (own rows + halo rows), W_0 = U_0^H U_0, T_0
+    if (!multi) {
+        EIGSOL_CUDA(cudaMemcpyAsync(d_xcol.p, x0, size_t(n) * K * s, cudaMemcpyHostToDevice, st));
+    } else {
+        const char* src = static_cast<const char*>(x0);
+        std::vector<char> hx(size_t(m.nhalo) * s);
+        for (int b = 0; b < K; ++b) {
+            const char* col = src + size_t(b) * size_t(nglob) * s;
+            char* dcol = d_xcol.as<char>() + size_t(b) * size_t(ext) * s;
+            if (n) EIGSOL_CUDA(cudaMemcpyAsync(dcol, col + size_t(m.lo) * s, size_t(n) * s, cudaMemcpyHostToDevice, st));
+            if (m.nhalo) {
+                for (int64_t k = 0; k < m.nhalo; ++k) std::memcpy(hx.data() + size_t(k) * s, col + size_t(m.halo.cols[size_t(k)]) * s, s);
+                EIGSOL_CUDA(cudaMemcpyAsync(dcol + size_t(m.nloc_pad) * s, hx.data(), hx.size(), cudaMemcpyHostToDevice, st));
+                EIGSOL_CUDA(cudaStreamSynchronize(st));  // hx is reused for the next column
+            }
+        }
+    }
+    const int gn = int((ext + B - 1) / B);
+    block_pack_kernel<S, K><<<gn, B, 0, st>>>(d_xcol.as<S>(), ext, ba.u[0]);
     BlockState* hs = h_state.as<BlockState>();
     std::memset(hs, 0, sizeof(BlockState));
     hs->k = K;
@@ -112,9 +236,10 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
     hs->sigma = m.sigma0;
     EIGSOL_CUDA(cudaMemcpyAsync(d_state.p, hs, sizeof(BlockState), cudaMemcpyHostToDevice, st));
     block_gram_kernel<S, K, B><<<grid, B, 0, st>>>(ba.u[0], n, ba.partials, grid);
-    block_control_kernel<1024><<<1, 1024, 0, st>>>(ba.st, ba.partials, grid, K, Sc<S>::is_complex ? 1 : 0, 1);
+    block_control_kernel<1024><<<1, 1024, 0, st>>>(ba.st, ba.partials, grid, K, Sc<S>::is_complex ? 1 : 0, 1, peer, ++epoch);
     EIGSOL_CUDA(cudaGetLastError());
     res.launches += 3;
+    int trip_no = 0;  // launch number of the next SpMM on the host side (the device counts in BlockState::launch_no)
 
     auto one_trip = [&] {
         if (m.dense) {
@@ -132,8 +257,16 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
             }
             res.launches += 2;
         }
+        if (peer) {
+            // the rows of the block just written that peers read -> their halo segments (buffer (L + 1) & 1)
+            const int gp = std::max(1, std::min(m.sm_count * 2, int((int64_t(std::max<int64_t>(m.nhalo, 1)) * K + B - 1) / B)));
+            launch_pdl(m.pdl, st, block_halo_push_kernel<S, K>, dim3(gp), dim3(B), 0, peer, static_cast<const S*>(ba.u[(trip_no + 1) & 1]),
+                       (trip_no + 1) & 1);
+            ++res.launches;
+        }
+        ++trip_no;
         launch_pdl(m.pdl, st, block_control_kernel<1024>, dim3(1), dim3(1024), 0, ba.st, ba.partials, grid, K,
-                   Sc<S>::is_complex ? 1 : 0, 0);
+                   Sc<S>::is_complex ? 1 : 0, 0, peer, ++epoch);
     };
 
     const int poll = std::max(1, env_int("EIGSOL_B200_BLOCK_POLL", 16));
@@ -156,6 +289,10 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
     EIGSOL_CUDA(cudaEventElapsedTime(&res.ms, m.ev0, m.ev1));
     m.launches += res.launches;
 
+    if (hs->stop == BSTOP_ERROR)
+        throw DeviceError("powerMethod: device error: a peer GPU did not signal within the timeout "
+                          "(EIGSOL_B200_PEER_TIMEOUT_MS); the ranks are out of step");
+    if (multi) comm_min_int(m.comm, 1);  // every rank is past its last launch before any buffer of this solve is freed
     res.iterations = hs->iterations;
     res.converged = hs->converged;
     res.breakdown = hs->stop == BSTOP_BREAKDOWN ? 1 : 0;
@@ -183,11 +320,17 @@ static void block_run_t(MatrixImpl& m, int nev, const void* x0, int max_it, doub
         }
     }
     const int f = std::max(hs->final_launch, 0);
-    block_finish_kernel<S, K><<<gn, B, 0, st>>>(ba.u[f & 1], bm, n, d_xcol.as<S>());
+    block_finish_kernel<S, K><<<gn, B, 0, st>>>(ba.u[f & 1], bm, ext, d_xcol.as<S>());
     EIGSOL_CUDA(cudaGetLastError());
     ++m.launches;
-    EIGSOL_CUDA(cudaMemcpyAsync(x_out, d_xcol.p, size_t(n) * K * s, cudaMemcpyDeviceToHost, st));
-    EIGSOL_CUDA(cudaStreamSynchronize(st));
+    if (!multi) {
+        EIGSOL_CUDA(cudaMemcpyAsync(x_out, d_xcol.p, size_t(n) * K * s, cudaMemcpyDeviceToHost, st));
+        EIGSOL_CUDA(cudaStreamSynchronize(st));
+    } else {
+        // column by column: own rows of every rank -> the global column of the caller's n x K block
+        for (int b = 0; b < K; ++b)
+            m.gather_download(d_xcol.as<char>() + size_t(b) * size_t(ext) * s, static_cast<char*>(x_out) + size_t(b) * size_t(nglob) * s);
+    }
 }
 
 template <class S>
@@ -204,7 +347,7 @@ static void block_run_k(MatrixImpl& m, int k, int nev, const void* x0, int max_i
 
 static void block_power_run(MatrixImpl& m, int k, int nev, const void* x0, int max_it, double tol, void* x_out,
                             double* lambda_out, BlockResult& res) {
-    if (m.nranks != 1) throw PlanError("the block power iteration runs on one GPU in this version");
+    if (m.nranks != 1 && m.dense) throw PlanError("the multi-GPU block power iteration handles sparse matrices (dense: one GPU)");
     if (nev < 1 || nev > k) throw PlanError("nev must satisfy 1 <= nev <= block width");
     if (!x0 || !lambda_out) throw PlanError("null pointer");
     EIGSOL_CUDA(cudaSetDevice(m.device));

@@ -388,7 +388,7 @@ EB_HDN bool eig_general(const Cx* H, int k, Cx* theta, Cx* S) {
 }
 
 // ---- the iteration state and its control step ---------------------------------------------------------
-enum { BSTOP_NONE = 0, BSTOP_CONVERGED = 1, BSTOP_BREAKDOWN = 2, BSTOP_MAX_TRIPS = 3 };
+enum { BSTOP_NONE = 0, BSTOP_CONVERGED = 1, BSTOP_BREAKDOWN = 2, BSTOP_MAX_TRIPS = 3, BSTOP_ERROR = 4 /* a peer GPU never arrived */ };
 
 struct BlockState {
     int k;            // block width

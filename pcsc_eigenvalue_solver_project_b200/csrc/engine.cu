@@ -1401,7 +1401,7 @@ void MatrixImpl::configure_launch() {
     if (dense) {
         const int RT = block * (dtype ? 1 : 2) * (gemv_var == 2 ? 2 : 1);  // rows per CTA (kernels.cuh: GemvRows)
         ntiles = int(std::max<int64_t>((nloc + RT - 1) / RT, 1));
-        const int target = sm_count * env_int("EIGSOL_B200_GEMV_WAVES", 4);
+        const int target = sm_count * env_int("EIGSOL_B200_GEMV_WAVES", 5);
         nseg = std::max(1, target / ntiles);
         nseg = int(std::min<int64_t>(nseg, std::max<int64_t>(1, (ext_len + 31) / 32)));
         grid = ntiles * nseg + 1;  // + the control CTA
@@ -2456,9 +2456,14 @@ int eigsol_b200_block_power_run(eigsol_b200_matrix* m, int block, int nev, const
     if (!m || !x0 || !lambda_out) return fail(EIGSOL_B200_ERR_INVALID, "eigsol_b200: invalid argument: null pointer");
     std::lock_guard<std::mutex> lock(m->mu);
     return guarded([&] {
-        if (m->group) throw PlanError("the block power iteration runs on one GPU in this version (EIGSOL_B200_NGPU=1)");
-        BlockResult r;
-        block_power_run(*m->one, block, nev, x0, max_iterations, tolerance, x_out, lambda_out, r);
+        BlockResult rr[kMaxPeers];
+        double lam[kMaxPeers][2 * kBlockMax];
+        m->each([&](MatrixImpl& impl, int k) {
+            // every rank of a group writes its own rows of x_out; the scalars come from rank 0 (identical everywhere)
+            block_power_run(impl, block, nev, x0, max_iterations, tolerance, x_out, lam[k], rr[k]);
+        });
+        const BlockResult& r = rr[0];
+        for (int i = 0; i < 2 * block; ++i) lambda_out[i] = lam[0][i];
         if (iterations_out) *iterations_out = r.iterations;
         if (converged_out) *converged_out = r.converged;
         if (breakdown_out) *breakdown_out = r.breakdown;

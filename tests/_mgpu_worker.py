@@ -115,6 +115,24 @@ def main():
     for rep in range(3):
         check(f"repeat {rep}", dm.power(x0, es.SolverOptions(17, -1.0)), ref)
 
+    # 5b. block power iteration on the sharded matrix (peer mode: CUDA IPC mappings of the block buffers, halo push after
+    #     every SpMM, Gram sums all-reduced in the control launch) against the CPU restatement on the whole matrix
+    if os.environ.get("EIGSOL_B200_EXPECT_EXCHANGE") == "peer":
+        import _blocksim as bs
+        a3 = sp.csr_matrix((v, ci, rp), shape=(n, n))
+        for k in (1, 4):
+            xb = es.random_block(n, k, np.float64, seed=5)
+            rb = dm.block_power(xb, k, es.SolverOptions(25, -1.0))
+            th, X, itb, _, _ = bs.block_power_cpu(lambda q: a3 @ q, xb, k, 25, -1.0)
+            q1, _ = np.linalg.qr(rb.eigenvectors)
+            q2, _ = np.linalg.qr(X)
+            ok = rb.iterations == itb == 25 and not rb.breakdown and np.allclose(rb.eigenvalues, th, rtol=1e-10) \
+                and np.linalg.norm(q1 @ (q1.conj().T @ q2) - q2) < 1e-8
+            if rank == 0:
+                print(f"[block k={k}] world={world} ritz0={rb.eigenvalues[0]!r} ref={th[0]!r} -> {'ok' if ok else 'FAIL'}", flush=True)
+            if not ok:
+                failures.append(f"block k={k}")
+
     # 6. a peer that stops taking part must surface as an error on the others, never as a hang (peer mode only)
     if os.environ.get("EIGSOL_B200_EXPECT_EXCHANGE") == "peer":
         dm.begin(x0, 1000, -1.0)  # collective
