@@ -9,6 +9,7 @@
 #include <chrono>
 #include <condition_variable>
 #include <functional>
+#include <map>
 #include <cstdio>
 #include <climits>
 #include <cstdlib>
@@ -1951,30 +1952,32 @@ void MatrixImpl::fill_info(eigsol_b200_matrix_info* info) const {
 // rank would -- the same partition, the same fused peer-memory kernel -- so that the reference-facing call
 // EigSol::powerMethod(M, opts) shards over the GPUs of the box without the caller knowing.
 // -------------------------------------------------------------------------------------------------
-struct LocalSolver {
+// The host threads, streams and meeting point of a group over devices [first, first + P) live for the life of the
+// process (thread start, stream creation and granting the peers access to the memory pools cost milliseconds -- more
+// than the 20 trips of a short solve); every group handle over the same devices borrows them, one job at a time.
+struct GroupWorkers {
     const int P;
     LocalGroup group;
     std::vector<int> devices;
     std::vector<std::unique_ptr<Comm>> comms;
-    std::vector<std::unique_ptr<MatrixImpl>> ranks;
     std::vector<std::thread> threads;
+    std::mutex job_mu;  // one job (of any handle) at a time: the ranks of two handles never interleave in the barriers
     std::mutex mu;
     std::condition_variable cv_work, cv_done;
     std::function<void(int)> job;
     uint64_t job_id = 0;
     int pending = 0;
-    bool quit = false;
     std::vector<std::exception_ptr> errors;
     std::vector<uint64_t> error_seq;
     uint64_t seq = 0;
 
-    LocalSolver(int nranks, int first_device) : P(nranks), group(nranks) {
+    GroupWorkers(int nranks, int first_device) : P(nranks), group(nranks) {
         for (int r = 0; r < P; ++r) devices.push_back(first_device + r);
         comms.resize(size_t(P));
-        ranks.resize(size_t(P));
         errors.resize(size_t(P));
         error_seq.assign(size_t(P), 0);
         for (int r = 0; r < P; ++r) threads.emplace_back([this, r] { worker(r); });
+        for (auto& t : threads) t.detach();  // they serve until the process exits
         run_all([this](int r) {
             std::unique_ptr<Comm> c(new Comm);
             c->rank = r;
@@ -2004,23 +2007,16 @@ struct LocalSolver {
                 c->pool_shared = ok && env_int("EIGSOL_B200_GROUP_POOL", 1) != 0;
             }
             comms[size_t(r)] = std::move(c);
-            ranks[size_t(r)].reset(new MatrixImpl);
         });
     }
-    ~LocalSolver() {
-        try {
-            run_all([this](int r) {
-                ranks[size_t(r)].reset();
-                comms[size_t(r)].reset();
-            });
-        } catch (...) {
-        }
-        {
-            std::lock_guard<std::mutex> lk(mu);
-            quit = true;
-        }
-        cv_work.notify_all();
-        for (auto& t : threads) t.join();
+    // process-wide, never destroyed (worker threads must not be joined during static destruction)
+    static GroupWorkers& get(int nranks, int first_device) {
+        static std::mutex mu;
+        static std::map<std::pair<int, int>, GroupWorkers*>* pools = new std::map<std::pair<int, int>, GroupWorkers*>();
+        std::lock_guard<std::mutex> lk(mu);
+        GroupWorkers*& w = (*pools)[{nranks, first_device}];
+        if (!w) w = new GroupWorkers(nranks, first_device);
+        return *w;
     }
     void worker(int r) {
         cudaSetDevice(devices[size_t(r)]);
@@ -2029,8 +2025,7 @@ struct LocalSolver {
             std::function<void(int)> fn;
             {
                 std::unique_lock<std::mutex> lk(mu);
-                cv_work.wait(lk, [&] { return quit || job_id != seen; });
-                if (quit) return;
+                cv_work.wait(lk, [&] { return job_id != seen; });
                 seen = job_id;
                 fn = job;
             }
@@ -2053,6 +2048,7 @@ struct LocalSolver {
     }
     // runs fn(rank) on every rank's thread; rethrows the FIRST failure (the later ones are its echoes)
     void run_all(std::function<void(int)> fn) {
+        std::lock_guard<std::mutex> one_job(job_mu);
         std::unique_lock<std::mutex> lk(mu);
         for (auto& e : errors) e = nullptr;
         seq = 0;
@@ -2069,6 +2065,26 @@ struct LocalSolver {
             std::rethrow_exception(errors[size_t(first)]);
         }
     }
+};
+
+struct LocalSolver {
+    const int P;
+    GroupWorkers& workers;
+    std::vector<std::unique_ptr<Comm>>& comms;  // the workers' (shared by every handle of the group)
+    std::vector<std::unique_ptr<MatrixImpl>> ranks;
+
+    LocalSolver(int nranks, int first_device)
+        : P(nranks), workers(GroupWorkers::get(nranks, first_device)), comms(workers.comms) {
+        ranks.resize(size_t(P));
+        run_all([this](int r) { ranks[size_t(r)].reset(new MatrixImpl); });
+    }
+    ~LocalSolver() {
+        try {
+            run_all([this](int r) { ranks[size_t(r)].reset(); });  // every rank frees its own device memory
+        } catch (...) {
+        }
+    }
+    void run_all(std::function<void(int)> fn) { workers.run_all(std::move(fn)); }
     MatrixImpl& r0() { return *ranks[0]; }
 };
 
@@ -2197,8 +2213,10 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
     return guarded([&] {
         if (!outer || (outer[cols] > 0 && (!inner || !values))) throw PlanError("null CSC array");
         std::unique_ptr<eigsol_b200_matrix> h(new eigsol_b200_matrix);
+        Trace tg;
         if (!comm) h->group = make_group(rows);
         if (h->group) {
+            tg.mark_async("group: workers ready");
             // column-slab boundaries from the column prefix `outer` (nnz-balanced), reused as the row partition
             if (outer[0] != 0) throw PlanError("CSC outer index must start at 0 (compressed storage expected)");
             for (int64_t j = 0; j < cols; ++j)
@@ -2212,6 +2230,7 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
                 m.preload_x0 = pre;
                 m.init_sparse_group_csc(rows, cols, outer, inner, values);
             });
+            tg.mark_async("group: ranks initialised");
             *out = h.release();
             ++g_matrices_created;
             return int(EIGSOL_B200_OK);
