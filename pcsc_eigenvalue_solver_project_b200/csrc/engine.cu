@@ -123,11 +123,14 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? std::atoi(v) : dflt;
 }
 
-// Host threads feeding the pinned staging buffers of an upload: half the cores, shared by the ranks that run on this
-// host (one GPU on a 16-core box: 2 threads 940 it/s on the one-shot C5 call, 4: 1100, 8: 1200), 1..8 per rank.
-static int upload_threads(int nranks) {
+// Host threads feeding the pinned staging buffers of an upload.  One GPU: half the cores (16-core box, one-shot C5 call:
+// 2 threads 940 it/s, 4: 1100, 8: 1200, 16: slower).  A single-process group: ALL cores divided by the ranks -- every
+// rank feeds its own PCIe link and the calling thread only waits (2 GPUs, 16 cores, 20-trip call: 4 per rank 67.8 ms,
+// 6: 61.7, 8: 59.3).  Process-per-GPU ranks share the host with their launcher's other work: half the cores / ranks.
+static int upload_threads(int nranks, bool local_group = false) {
     const unsigned hw = std::max(2u, std::thread::hardware_concurrency());
-    const int dflt = int(std::min(8u, std::max(1u, hw / 2 / unsigned(std::max(nranks, 1)))));
+    const unsigned share = local_group ? hw / unsigned(std::max(nranks, 1)) : hw / 2 / unsigned(std::max(nranks, 1));
+    const int dflt = int(std::min(8u, std::max(1u, share)));
     return std::max(1, env_int("EIGSOL_B200_UPLOAD_THREADS", std::max(dflt, nranks == 1 ? 2 : 1)));
 }
 
@@ -855,7 +858,7 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
             EIGSOL_CUDA(cudaStreamSynchronize(stream));
             up.add(d_x0pre.p, static_cast<const char*>(preload_x0) + size_t(lo) * s, size_t(nloc) * s);
         }
-        EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+        EIGSOL_CUDA(up.run(device, upload_threads(nranks, true)));
         x0_preloaded = preload_x0 != nullptr;
     }
     tr.mark("group csc: slab upload");
@@ -1020,7 +1023,7 @@ void MatrixImpl::init_sparse_device_rows(const int32_t* rowptr, const int32_t* c
     up.add(d_rowptr.p, rowptr, sizeof(int32_t) * size_t(nloc + 1));
     up.add(d_colidx.p, colidx + base, sizeof(int32_t) * size_t(nnz));
     up.add(d_vals.p, static_cast<const char*>(values) + size_t(base) * s, size_t(nnz) * s);
-    EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+    EIGSOL_CUDA(up.run(device, upload_threads(nranks, comm && comm->local)));
     if (base != 0) {
         const unsigned g = unsigned((nloc + 1 + 255) / 256);
         rebase_kernel<<<g, 256, 0, stream>>>(d_rowptr.as<int32_t>(), nloc + 1, base);
@@ -1612,7 +1615,7 @@ void MatrixImpl::begin(const void* x0, int max_it, double tol, bool unit_scale) 
             EIGSOL_CUDA(cudaStreamSynchronize(stream));  // the zero fill above must not land after the upload
             StagedUploader up;
             up.add(buf[0].p, src, size_t(nloc) * s);
-            EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+            EIGSOL_CUDA(up.run(device, upload_threads(nranks, comm && comm->local)));
         } else {
             EIGSOL_CUDA(cudaMemcpyAsync(buf[0].p, src, size_t(nloc) * s, cudaMemcpyHostToDevice, stream));
         }
@@ -1815,7 +1818,7 @@ void MatrixImpl::gather_download(const void* d_local, void* host_out) {
             StagedUploader down;  // device -> pinned -> pageable host array, several threads
             down.download = true;
             down.add(dst, src, bytes);
-            EIGSOL_CUDA(down.run(device, upload_threads(nranks)));
+            EIGSOL_CUDA(down.run(device, upload_threads(nranks, comm && comm->local)));
         } else if (bytes) {
             EIGSOL_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream));
             EIGSOL_CUDA(cudaStreamSynchronize(stream));

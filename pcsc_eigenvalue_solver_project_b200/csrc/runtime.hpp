@@ -96,22 +96,10 @@ struct DevBuf {
         EIGSOL_CUDA(cudaMemset(p, 0, n + pad));
         EIGSOL_CUDA(cudaDeviceSynchronize());
     }
-    // The default: zero-filled memory from the device's stream-ordered pool, ready for use on ANY stream when the call
-    // returns (allocation and fill run on the calling thread's own stream, which is then synchronised -- no
-    // device-wide synchronisation, no driver round trip once the pool is warm).
-    void alloc(size_t n, size_t pad = 64) {
-        release();
-        bytes = n;
-        if (cudaMallocAsync(&p, n + pad, cudaStreamPerThread) != cudaSuccess) {
-            cudaGetLastError();
-            p = nullptr;
-            alloc_plain(n, pad);
-            return;
-        }
-        pooled = true;
-        EIGSOL_CUDA(cudaMemsetAsync(p, 0, n + pad, cudaStreamPerThread));
-        EIGSOL_CUDA(cudaStreamSynchronize(cudaStreamPerThread));
-    }
+    // The default for small buffers: plain, zero-filled, synchronised.  (Routing these through cudaMallocAsync on the
+    // calling thread's per-thread stream was measured on a 2-GPU group: the setup phase that allocates the mailboxes
+    // went from 0.4 ms to 32 ms -- per-thread streams synchronise with the legacy stream the plain copies use.)
+    void alloc(size_t n, size_t pad = 64) { alloc_plain(n, pad); }
     // no zero fill, no synchronisation: for buffers every byte of which is written before it is read
     void alloc_raw(size_t n, size_t pad = 64) {
         release();
