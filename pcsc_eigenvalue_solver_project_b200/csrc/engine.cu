@@ -858,6 +858,7 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
             EIGSOL_CUDA(cudaStreamSynchronize(stream));
             up.add(d_x0pre.p, static_cast<const char*>(preload_x0) + size_t(lo) * s, size_t(nloc) * s);
         }
+        tr.mark_async("group csc: slab buffers");
         EIGSOL_CUDA(up.run(device, upload_threads(nranks, true)));
         x0_preloaded = preload_x0 != nullptr;
     }
@@ -990,6 +991,7 @@ void MatrixImpl::init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t
     }
     tr.mark("group csc: transpose");
     finish_rows_on_device();
+    tr.mark_async("group csc: finish returned");
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -2227,7 +2229,9 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
             const std::vector<int64_t> rb = partition_rows(cols, outer, h->group->P);
             const void* pre = g_preload_x0;  // (thread-local of the calling thread: hand it to the rank threads)
             h->each([&](MatrixImpl& m, int r) {
+                Trace tr;
                 m.init_common(dtype, h->group->comms[size_t(r)].get());
+                tr.mark_async("group rank: streams + state");
                 m.n = rows;
                 m.row_begin = rb;
                 m.preload_x0 = pre;

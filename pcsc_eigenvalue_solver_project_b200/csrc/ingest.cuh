@@ -17,6 +17,9 @@
 #include <stdint.h>
 
 #include <atomic>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <condition_variable>
 #include <cstdlib>
 #include <cstring>
@@ -73,6 +76,35 @@ struct PinnedPool {
 // order they were added.  start() returns at once; wait_prefix(k) blocks until the first k jobs have landed (so device
 // work that needs only those can start while the rest is still in flight); finish() joins and returns the first CUDA
 // error seen.  download = true reverses the direction (device -> pinned -> host array).
+// Host copy of one chunk into a pinned staging buffer.  EIGSOL_B200_STAGE_NT=1: non-temporal 16-byte stores (the
+// destination is only read by the DMA engine, so the lines need not be fetched nor kept in the caches of the core).
+inline void stage_copy(void* dst, const void* src, size_t bytes) {
+#if defined(__SSE2__)
+    static const bool nt = [] {
+        const char* e = std::getenv("EIGSOL_B200_STAGE_NT");
+        return e && *e && std::atoi(e) != 0;
+    }();
+    if (nt && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+        const size_t blocks = bytes / 64;
+        const __m128i* s = static_cast<const __m128i*>(src);
+        __m128i* d = static_cast<__m128i*>(dst);
+        for (size_t i = 0; i < blocks; ++i) {
+            const __m128i a = _mm_loadu_si128(s + 4 * i), b = _mm_loadu_si128(s + 4 * i + 1);
+            const __m128i c = _mm_loadu_si128(s + 4 * i + 2), e = _mm_loadu_si128(s + 4 * i + 3);
+            _mm_stream_si128(d + 4 * i, a);
+            _mm_stream_si128(d + 4 * i + 1, b);
+            _mm_stream_si128(d + 4 * i + 2, c);
+            _mm_stream_si128(d + 4 * i + 3, e);
+        }
+        _mm_sfence();
+        const size_t done = blocks * 64;
+        if (done < bytes) std::memcpy(static_cast<char*>(dst) + done, static_cast<const char*>(src) + done, bytes - done);
+        return;
+    }
+#endif
+    std::memcpy(dst, src, bytes);
+}
+
 struct StagedUploader {
     // bytes per job: small enough that the first DMA starts early and the tail is short, large enough that the per-job
     // cost (one cudaMemcpyAsync + one event) vanishes; EIGSOL_B200_UPLOAD_CHUNK_MB in [1, 16], default 4
@@ -156,7 +188,7 @@ struct StagedUploader {
                 e = cudaMemcpyAsync(pin[b], j.src, j.bytes, cudaMemcpyDeviceToHost, st);
                 pending[b] = &j;
             } else {
-                std::memcpy(pin[b], j.src, j.bytes);
+                stage_copy(pin[b], j.src, j.bytes);
                 e = cudaMemcpyAsync(j.dst, pin[b], j.bytes, cudaMemcpyHostToDevice, st);
             }
             if (e == cudaSuccess) e = cudaEventRecord(ev[b], st);
