@@ -374,7 +374,7 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
     scalar_block = env_int("EIGSOL_B200_SCALAR_BLOCK", 256) == 128 ? 128 : 256;
-    gemv_var = std::max(0, std::min(2, env_int("EIGSOL_B200_GEMV_VAR", 0)));
+    gemv_var = std::max(0, std::min(3, env_int("EIGSOL_B200_GEMV_VAR", 0)));
     gemv_map = env_int("EIGSOL_B200_GEMV_MAP", 0) ? 1 : 0;
     h_state.alloc(sizeof(PowerState));
 }
@@ -1556,11 +1556,13 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     const dim3 g(m.grid), b(B);
     auto go = [&](auto kern) { launch_pdl(m.pdl, m.stream, kern, g, b, 0, A, it, ph); };
     if (m.xmode == MODE_PEER) {
-        if (m.gemv_var == 2) go(gemv_colmajor_kernel<S, B, true, 2>);
+        if (m.gemv_var == 3) go(gemv_colmajor_kernel<S, B, true, 3>);
+        else if (m.gemv_var == 2) go(gemv_colmajor_kernel<S, B, true, 2>);
         else if (m.gemv_var == 1) go(gemv_colmajor_kernel<S, B, true, 1>);
         else go(gemv_colmajor_kernel<S, B, true, 0>);
     } else {
-        if (m.gemv_var == 2) go(gemv_colmajor_kernel<S, B, false, 2>);
+        if (m.gemv_var == 3) go(gemv_colmajor_kernel<S, B, false, 3>);
+        else if (m.gemv_var == 2) go(gemv_colmajor_kernel<S, B, false, 2>);
         else if (m.gemv_var == 1) go(gemv_colmajor_kernel<S, B, false, 1>);
         else go(gemv_colmajor_kernel<S, B, false, 0>);
     }

@@ -1029,9 +1029,34 @@ __global__ void __launch_bounds__(BLOCK) spmv_sell_kernel(SellView<S> A, IterArg
 // segment order (deterministic), runs the row epilogue and leaves the tile's sums in the tile's slot.
 // =================================================================================================
 constexpr int kGemvChunk = 512;  // columns of x staged per pass
-template <class S, int VAR> struct GemvRows { static constexpr int value = (Sc<S>::is_complex ? 1 : 2) * (VAR == 2 ? 2 : 1); };
+template <class S, int VAR> struct GemvRows { static constexpr int value = (Sc<S>::is_complex ? 1 : 2) * (VAR == 2 ? 2 : 1); };  // VAR 3 = VAR 0 rows
 
-// VAR 0: x staged 512 columns at a time, 8 column loads in flight per thread.  VAR 1: 64 columns, 4 loads in flight
+// Sum of the nseg segment partials of R consecutive rows, eight segments in flight, added in segment order.  Kept out
+// of line on purpose: inlined into the kernel, its registers ended up costing loads in flight in the streaming loop
+// (107 vs 91 us on C3).
+template <class S, int R>
+__device__ __noinline__ void gemv_combine_rows(const S* __restrict__ pp, int64_t lda, int nseg, S (&z)[R]) {
+#pragma unroll
+    for (int k = 0; k < R; ++k) z[k] = Sc<S>::zero();
+    int s0 = 0;
+    for (; s0 + 8 <= nseg; s0 += 8) {
+        S t[8][R];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int k = 0; k < R; ++k) t[i][k] = Sc<S>::ldcg(pp + int64_t(s0 + i) * lda + k);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int k = 0; k < R; ++k) Sc<S>::add(z[k], t[i][k]);
+    }
+    for (; s0 < nseg; ++s0)
+#pragma unroll
+        for (int k = 0; k < R; ++k) Sc<S>::add(z[k], Sc<S>::ldcg(pp + int64_t(s0) * lda + k));
+}
+
+// VAR 0: x staged 512 columns at a time, 8 column loads in flight per thread.  VAR 3: the same loop with the combine of
+// the last CTA done by gemv_combine_rows (eight partial loads in flight, out of line).  VAR 1: 64 columns, 4 loads in flight
 // (fewer registers).  A.tile_major selects which neighbours a CTA has in the launch order: 0 = the column segments of
 // one row tile, 1 = the row tiles of one column segment (adjacent CTAs then read adjacent 4 KB pieces of the SAME
 // columns, i.e. whole contiguous columns between them).
@@ -1044,8 +1069,8 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     }
     constexpr int R = GemvRows<S, VAR>::value;  // rows per thread: 16 bytes (VAR 0, 1) or 32 bytes (VAR 2) per column
     constexpr int RT = BLOCK * R;
-    constexpr int CHUNK = VAR == 0 ? kGemvChunk : (VAR == 1 ? 64 : 128);
-    constexpr int UNROLL = VAR == 0 ? 8 : 4;
+    constexpr int CHUNK = (VAR == 0 || VAR == 3) ? kGemvChunk : (VAR == 1 ? 64 : 128);
+    constexpr int UNROLL = (VAR == 0 || VAR == 3) ? 8 : 4;
     __shared__ __align__(16) S xs[CHUNK];
     __shared__ int s_tile_last;
     __shared__ SendSm sends;
@@ -1111,13 +1136,23 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
     __threadfence();
     // The tail of the launch: the last CTA of a row tile adds the segment partials (L2-resident) in segment order.
     double are = 0.0, aim = 0.0, qn = 0.0;
+    if constexpr (VAR == 3) {
+        if (live) {
+            S z[R];
+            gemv_combine_rows<S, R>(A.partial + r, A.lda, A.nseg, z);
 #pragma unroll
-    for (int k = 0; k < R; ++k) {
-        const int row = r + k;
-        if (row < A.rows) {
-            S z = Sc<S>::zero();
-            for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
-            row_epilogue<S>(sends, z, ld_x<S, PEER>(u, row), out, row, are, aim, qn);
+            for (int k = 0; k < R; ++k)
+                if (r + k < A.rows) row_epilogue<S>(sends, z[k], ld_x<S, PEER>(u, r + k), out, r + k, are, aim, qn);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            const int row = r + k;
+            if (row < A.rows) {
+                S z = Sc<S>::zero();
+                for (int sgi = 0; sgi < A.nseg; ++sgi) Sc<S>::add(z, Sc<S>::ldcg(A.partial + int64_t(sgi) * A.lda + row));
+                row_epilogue<S>(sends, z, ld_x<S, PEER>(u, row), out, row, are, aim, qn);
+            }
         }
     }
     cta_finish<S, BLOCK>(it, c, are, aim, qn, tile);

@@ -242,7 +242,7 @@ def test_dense_sizes(orc, n, cplx):
     dm.close()
 
 
-@pytest.mark.parametrize("var", [0, 1, 2])
+@pytest.mark.parametrize("var", [0, 1, 2, 3])
 @pytest.mark.parametrize("tile_major", [0, 1])
 @pytest.mark.parametrize("cplx", [False, True])
 def test_dense_kernel_variants(orc, monkeypatch, var, tile_major, cplx):
