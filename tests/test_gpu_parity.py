@@ -494,3 +494,34 @@ def test_matrix_device_cache_uploads_once_and_never_goes_stale(orc):
     es.powerMethod(D, es.SolverOptions(10, -1.0), x0=x0)
     check_result(es.powerMethod(D, es.SolverOptions(25, -1.0), x0=x0), orc.power_dense(a, x0, 25, -1.0))
     assert es.matrices_created() - before == 1
+
+
+def test_two_handles_from_two_threads(orc):
+    """Calls on different handles are independent (per-handle locks, no process-wide lock): two host threads solve on
+    two matrices at the same time and both get the oracle's answer."""
+    import threading
+    cases = []
+    for seed, g in ((1, 40), (2, 33)):
+        n = g * g
+        rp, ci, v = gen.laplacian_2d(g)
+        v = v.copy()
+        v[0] += seed
+        outer, inner, cv = general_csc(n, rp, ci, v)
+        x0 = orc.random_unit(n, np.float64, seed=seed)
+        cases.append((n, outer, inner, cv, x0, es.DeviceMatrix.from_matrix(es.Matrix(((n, n), outer, inner, cv)))))
+    out = [None, None]
+
+    def work(i):
+        n, outer, inner, cv, x0, dm = cases[i]
+        out[i] = [dm.power(x0, es.SolverOptions(400, -1.0)) for _ in range(5)]
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    for i, (n, outer, inner, cv, x0, dm) in enumerate(cases):
+        ref = orc.power_csc((n, n), outer, inner, cv, x0, 400, -1.0)
+        for r in out[i]:
+            check_result(r, ref)
+        dm.close()

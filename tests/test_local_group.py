@@ -179,3 +179,20 @@ def test_block_power_iteration_on_a_group(orc, ngpu, k, cplx):
         assert st == 0 and iters == 30
         assert abs(r.eigenvalues[0] - lam) <= LAMBDA_RTOL * abs(lam)
         assert phase_aligned_error(r.eigenvectors[:, 0], x) <= VECTOR_ATOL
+
+
+def test_group_rejects_malformed_input_and_recovers(orc, ngpu):
+    """A failure inside one rank's thread (row index out of range found on the device) comes back as the same error a
+    single GPU gives -- the other ranks leave their barriers instead of hanging -- and the group's workers are usable
+    for the next matrix."""
+    g = 12
+    n = g ** 3
+    rp, ci, v = gen.laplacian_3d(g)
+    outer, inner, cv = gen.csr_to_csc_hermitian(rp, ci, v)
+    bad = inner.copy()
+    bad[len(bad) // 2] = n + 7
+    with pytest.raises(ValueError, match="inner index out of range"):
+        es.DeviceMatrix.from_matrix(es.Matrix(((n, n), outer, bad, cv)))
+    x0 = orc.random_unit(n, np.float64, seed=9)
+    check(es.powerMethod(es.Matrix(((n, n), outer, inner, cv)), es.SolverOptions(25, -1.0), x0=x0),
+          orc.power_csc((n, n), outer, inner, cv, x0, 25, -1.0))
