@@ -93,6 +93,10 @@ Matrix readInsideSparseMatrix(std::ifstream& in, int rows, int cols) {
     }
     Matrix::Sparse<Scalar> a(rows, cols);
     a.setFromTriplets(entries.begin(), entries.end());  // sorted, compressed: O(nnz) instead of insert() per entry
+    // setFromTriplets SUMS repeated (row, column) pairs; the reference's SparseMatrix::insert forbids them (an assertion
+    // in debug builds, a corrupt matrix otherwise) and the fast reader behind readMatrixFromFile rejects them: same here
+    if (a.nonZeros() != static_cast<Eigen::Index>(entries.size()))
+        throw std::runtime_error("Duplicate (row, column) entry in sparse matrix");
     return Matrix(a);
 }
 

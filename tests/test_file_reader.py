@@ -305,3 +305,16 @@ def test_cxx_header_raises_the_reference_messages(tmp_path, kind, text, message)
         f.write(text)
     rc, err, _ = cxx_read(p, kind, tmp_path)
     assert rc == 3 and err == message
+
+
+def test_duplicate_entries_are_rejected_by_every_reader_path(tmp_path):
+    """A repeated (row, column) pair: the reference's SparseMatrix::insert forbids it.  The fast reader (double /
+    complex<double>, also behind the Python wrapper) and the drop-in header's stream path (other scalars, here float)
+    answer with the same error."""
+    p = str(tmp_path / "dup.txt")
+    open(p, "w").write("sparse\n3 3 4\n0 0 1.0\n1 1 2.0\n0 0 3.0\n2 2 4.0\n")
+    with pytest.raises(RuntimeError, match="Duplicate \\(row, column\\)"):
+        es.readMatrixFromFile(p, np.float64)
+    for kind in ("d", "f"):
+        rc, err, _ = cxx_read(p, kind, tmp_path)
+        assert rc == 3 and "Duplicate (row, column)" in err, (kind, rc, err)
