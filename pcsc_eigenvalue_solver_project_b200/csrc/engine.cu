@@ -253,6 +253,9 @@ struct MatrixImpl {
     int serpentine = 0;
     bool pdl = true;  // programmatic dependent launch of the matvec kernels
     int scalar_block = 256;  // EIGSOL_B200_SCALAR_BLOCK: threads per CTA (= rows per work unit) of csr_scalar
+    int dense_sym = 0;  // one GPU, dense: 1 = A == A^T, 2 = A == A^H (bitwise, checked at upload) -> gemv_sym_kernel
+    int64_t sym_per = 0;
+    int sym_nwarps = 0;
     int gemv_map = 0;  // EIGSOL_B200_GEMV_MAP: 1 = row tiles of one column segment are neighbouring CTAs
     int gemv_var = 0;  // EIGSOL_B200_GEMV_VAR: streaming loop variant of the dense kernel (kernels.cuh)
 
@@ -303,6 +306,7 @@ struct MatrixImpl {
     double near_diag_on_device(int64_t row0);
     void init_sparse_group_csc(int64_t rows, int64_t cols, const int32_t* outer, const int32_t* inner, const void* values);
     void init_dense(int64_t rows, const void* a, int64_t lda_host);
+    void check_dense_symmetry();
     void plan_exchange();
     void setup_peer();
     template <class S> IterArgs<S> iter_args() {
@@ -374,7 +378,7 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     serpentine = env_int("EIGSOL_B200_SERPENTINE", 1) ? 1 : 0;
     pdl = env_int("EIGSOL_B200_PDL", 1) != 0;
     scalar_block = env_int("EIGSOL_B200_SCALAR_BLOCK", 256) == 128 ? 128 : 256;
-    gemv_var = std::max(0, std::min(3, env_int("EIGSOL_B200_GEMV_VAR", 0)));
+    gemv_var = std::max(0, std::min(3, env_int("EIGSOL_B200_GEMV_VAR", 3)));
     gemv_map = env_int("EIGSOL_B200_GEMV_MAP", 0) ? 1 : 0;
     h_state.alloc(sizeof(PowerState));
 }
@@ -1347,6 +1351,7 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
         StagedUploader up;
         up.add(d_dense.p, src, size_t(n) * size_t(n) * s);
         EIGSOL_CUDA(up.run(device, upload_threads(nranks)));
+        check_dense_symmetry();
         set_kernel(K_GEMV, 0);
         compute_prescale();
         return;
@@ -1362,8 +1367,30 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
     copy_cols(0, lo, nloc_pad);
     copy_cols(hi, n - hi, nloc_pad + lo);
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    check_dense_symmetry();
     set_kernel(K_GEMV, 0);
     compute_prescale();
+}
+
+// One GPU: is the resident dense matrix bitwise equal to its transpose / conjugate transpose?  Then the matvec can read
+// the stored columns as rows (gemv_sym_kernel).  EIGSOL_B200_GEMV_SYM=0 switches the test (and that kernel) off.
+void MatrixImpl::check_dense_symmetry() {
+    dense_sym = 0;
+    if (nranks != 1 || n < 1 || !env_int("EIGSOL_B200_GEMV_SYM", 1)) return;
+    DevBuf d_flags;
+    d_flags.alloc(64);
+    int three = 3;
+    EIGSOL_CUDA(cudaMemcpyAsync(d_flags.p, &three, sizeof three, cudaMemcpyHostToDevice, stream));
+    const unsigned t = unsigned((n + 31) / 32);
+    if (dtype) sym_check_kernel<double2><<<dim3(t, t), 256, 0, stream>>>(d_dense.as<double2>(), int(n), lda, d_flags.as<int>());
+    else sym_check_kernel<double><<<dim3(t, t), 256, 0, stream>>>(d_dense.as<double>(), int(n), lda, d_flags.as<int>());
+    ++launches;
+    EIGSOL_CUDA(cudaGetLastError());
+    int f = 0;
+    EIGSOL_CUDA(cudaMemcpyAsync(&f, d_flags.p, sizeof f, cudaMemcpyDeviceToHost, stream));
+    EIGSOL_CUDA(cudaStreamSynchronize(stream));
+    if (f & 2) dense_sym = 2;       // Hermitian (a real symmetric matrix is both: the conjugate is a no-op)
+    else if (f & 1) dense_sym = 1;  // complex symmetric
 }
 
 // -------------------------------------------------------------------------------------------------
@@ -1404,7 +1431,23 @@ void MatrixImpl::configure_launch() {
     // quantisation of a small per-rank problem over the persistent grid (8 GPUs on C5: 9.2 units of 256 rows per CTA)
     block = (!dense && kernel == K_CSR_SCALAR && scalar_block == 128) ? 128 : 256;
     const int64_t s = ss();
-    if (dense) {
+    if (dense && dense_sym && nranks == 1) {
+        // flat, perfectly balanced partition of the stored matrix over the warps of a persistent grid (gemv_sym_kernel)
+        const int occ = dtype ? occupancy(gemv_sym_kernel<double2, 256>, 256) : occupancy(gemv_sym_kernel<double, 256>, 256);
+        const int64_t total = lda * n;
+        int64_t nw = std::min<int64_t>(int64_t(sm_count) * occ * (block / 32), n);  // every warp at least one column long
+        int64_t per = ((total + nw - 1) / nw + 127) / 128 * 128;
+        per = std::max<int64_t>(per, (lda + 127) / 128 * 128);
+        nw = (total + per - 1) / per;
+        sym_per = per;
+        sym_nwarps = int(nw);
+        nslots = int((nw + block / 32 - 1) / (block / 32));
+        grid = nslots + 1;
+        ntiles = int(n);  // tickets: one per column
+        d_dense_partial.alloc(size_t(2) * size_t(n) * size_t(s));
+        d_tile_ticket.alloc(sizeof(unsigned) * size_t(n));
+        stored_bytes = s * lda * n + 2 * s * n;
+    } else if (dense) {
         const int RT = block * (dtype ? 1 : 2) * (gemv_var == 2 ? 2 : 1);  // rows per CTA (kernels.cuh: GemvRows)
         ntiles = int(std::max<int64_t>((nloc + RT - 1) / RT, 1));
         const int target = sm_count * env_int("EIGSOL_B200_GEMV_WAVES", 5);
@@ -1554,6 +1597,12 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
     DenseView<S> A{int32_t(m.nloc), int32_t(m.ext_len), m.lda, m.d_dense.as<S>(), m.nseg, m.ntiles,
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>(), m.gemv_map};
     const dim3 g(m.grid), b(B);
+    if (m.dense_sym && m.nranks == 1) {
+        SymDenseView<S> V{int32_t(m.n), m.lda, m.d_dense.as<S>(), m.sym_per, m.sym_nwarps, m.d_dense_partial.as<S>(),
+                          m.d_tile_ticket.as<unsigned>(), m.dense_sym == 2 ? 1 : 0};
+        launch_pdl(m.pdl, m.stream, gemv_sym_kernel<S, B>, g, b, 0, V, it, ph);
+        return;
+    }
     auto go = [&](auto kern) { launch_pdl(m.pdl, m.stream, kern, g, b, 0, A, it, ph); };
     if (m.xmode == MODE_PEER) {
         if (m.gemv_var == 3) go(gemv_colmajor_kernel<S, B, true, 3>);

@@ -1159,6 +1159,157 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
 }
 
 // =================================================================================================
+// Dense GEMV for a matrix that equals its own (conjugate) transpose: y_j = sum_i op(A[i,j]) x_i, op = conj for a
+// Hermitian matrix, identity for a symmetric one -- the dot product of the STORED column j with x.  The column-major
+// array is then read as one flat stream: warp w owns the elements [w * per, (w + 1) * per) (a multiple of 128, at
+// least one column long), walks them with 32-byte loads (SASS LDG.E.ENL2.256), keeps x in L1, and reduces every column
+// with shuffles alone -- no column-segment partials of the whole vector, no shared memory, no last-CTA combine.  All
+// warps carry the same number of bytes (+-1 KB), so they finish together.  Only the column a range starts or ends in
+// the middle of is shared by two warps: its two partial sums are added, in row order, by whichever warp arrives second
+// (one ticket per column).  The engine selects this kernel when a bitwise symmetry check at upload succeeds
+// (sym_check_kernel); everything else of the launch (control CTA, state machine, epilogue sums) is the common frame.
+// One GPU only (the row blocks of a sharded dense matrix are not symmetric).
+// =================================================================================================
+template <class S> struct SymDenseView {
+    int32_t n;            // order of the matrix
+    int64_t lda;          // device leading dimension (multiple of 16, rows >= n are zero)
+    const S* a;           // column-major
+    int64_t per;          // elements per warp (multiple of 128, >= lda)
+    int32_t nwarps;       // warps that own a range
+    S* partial;           // [n][2]: partial sums of the columns shared by two warps (head part, tail part)
+    unsigned* ticket;     // [n]
+    int32_t conj;         // 1: Hermitian (use conj of the stored entries)
+};
+
+template <class S> __device__ __forceinline__ void ld_stream_row4(const S* p, S (&o)[32 / sizeof(S)]);
+template <> __device__ __forceinline__ void ld_stream_row4<double>(const double* p, double (&o)[4]) { ld_stream_f64x4(p, o); }
+template <> __device__ __forceinline__ void ld_stream_row4<double2>(const double2* p, double2 (&o)[2]) {
+    double t[4];
+    ld_stream_f64x4(reinterpret_cast<const double*>(p), t);
+    o[0] = make_double2(t[0], t[1]);
+    o[1] = make_double2(t[2], t[3]);
+}
+
+template <class S, int BLOCK>
+__global__ void __launch_bounds__(BLOCK) gemv_sym_kernel(SymDenseView<S> A, IterArgs<S> it, int phase) {
+    pdl_prologue();
+    if (blockIdx.x == 0) {
+        control_cta<S, BLOCK>(it, true);
+        return;
+    }
+    constexpr int V = 32 / int(sizeof(S));  // elements per 32-byte load: 4 real, 2 complex
+    constexpr int STEP = 32 * V;            // elements per warp instruction
+    __shared__ SendSm sends;
+    LaunchCtx c;
+    if (!launch_begin<S>(it, phase, c)) return;
+    load_sends<S>(it, c, sends);  // (no sends on one GPU; keeps the common epilogue)
+    const S* __restrict__ u = ring_buf<S>(it, c.in);
+    S* __restrict__ out = ring_buf<S>(it, c.out);
+    const int lane = threadIdx.x & 31;
+    const int gw = (int(blockIdx.x) - 1) * (BLOCK / 32) + (threadIdx.x >> 5);
+    double are = 0.0, aim = 0.0, qn = 0.0;
+    if (gw < A.nwarps) {
+        const int64_t total = A.lda * int64_t(A.n);
+        int64_t e = int64_t(gw) * A.per;
+        const int64_t e_end = min(total, e + A.per);
+        while (e < e_end) {
+            const int col = int(e / A.lda);
+            const int64_t r0 = e - int64_t(col) * A.lda;
+            const int64_t r1 = min(A.lda, r0 + (e_end - e));  // rows [r0, r1) of column `col`
+            const S* ap = A.a + int64_t(col) * A.lda;
+            S acc[V];
+#pragma unroll
+            for (int k = 0; k < V; ++k) acc[k] = Sc<S>::zero();
+            int64_t i = r0 + int64_t(lane) * V;
+#pragma unroll 4
+            for (; i + V <= r1; i += STEP) {
+                S a[V], x[V];
+                ld_stream_row4<S>(ap + i, a);
+                {
+                    // the matching 32 bytes of x, through L1 (x is read by every warp over and over)
+                    const double2* xp = reinterpret_cast<const double2*>(u + i);
+                    const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
+                    if constexpr (Sc<S>::is_complex) {
+                        x[0] = xa;
+                        x[1] = xb;
+                    } else {
+                        x[0] = xa.x;
+                        x[1] = xa.y;
+                        x[2] = xb.x;
+                        x[3] = xb.y;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    if constexpr (Sc<S>::is_complex) {
+                        if (A.conj) a[k].y = -a[k].y;
+                    }
+                    Sc<S>::mac(acc[k], a[k], x[k]);
+                }
+            }
+            S sum = acc[0];
+#pragma unroll
+            for (int k = 1; k < V; ++k) Sc<S>::add(sum, acc[k]);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) Sc<S>::add(sum, Sc<S>::shfl_down(sum, d, 32));
+            if (lane == 0) {
+                const bool head = r0 == 0, tail = r1 == A.lda;
+                bool finalize = head && tail;
+                S z = sum;
+                if (!finalize) {
+                    // a column shared with the neighbouring warp: the second to arrive adds head + tail (row order)
+                    A.partial[2 * int64_t(col) + (head ? 0 : 1)] = sum;
+                    __threadfence();
+                    const unsigned t = atomicAdd(A.ticket + col, 1u);
+                    if (t == 1u) {
+                        A.ticket[col] = 0;
+                        __threadfence();
+                        z = Sc<S>::ldcg(A.partial + 2 * int64_t(col));
+                        Sc<S>::add(z, Sc<S>::ldcg(A.partial + 2 * int64_t(col) + 1));
+                        finalize = true;
+                    }
+                }
+                if (finalize) row_epilogue<S>(sends, Sc<S>::scale(z, c.s), Sc<S>::ldg(u + col), out, col, are, aim, qn);
+            }
+            e += r1 - r0;
+        }
+    }
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
+}
+
+// Bitwise test A == A^T (flags bit 0 cleared if not) and A == A^H (bit 1 cleared if not) of a column-major n x n matrix:
+// 32 x 32 tiles of the upper triangle against their mirror tiles, both read coalesced through shared memory.
+template <class S>
+__global__ void __launch_bounds__(256) sym_check_kernel(const S* __restrict__ a, int n, int64_t lda, int* flags) {
+    __shared__ S tile[32][33];
+    const int tj = blockIdx.x, ti = blockIdx.y;
+    if (ti > tj) return;  // upper triangle of tiles (ti <= tj)
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    // mirror tile (rows of tile tj, columns of tile ti), element (r, c) = a[tj*32 + r + (ti*32 + c) * lda]
+    for (int cc = ty; cc < 32; cc += 8) {
+        const int r = tj * 32 + tx, cidx = ti * 32 + cc;
+        tile[cc][tx] = (r < n && cidx < n) ? a[r + int64_t(cidx) * lda] : Sc<S>::zero();
+    }
+    __syncthreads();
+    int bad_sym = 0, bad_herm = 0;
+    for (int cc = ty; cc < 32; cc += 8) {
+        const int r = ti * 32 + tx, cidx = tj * 32 + cc;  // element (r, cidx) of the upper tile; its mirror is tile[tx][cc]
+        if (r < n && cidx < n) {
+            const S v = a[r + int64_t(cidx) * lda];
+            const S m = tile[tx][cc];
+            if constexpr (Sc<S>::is_complex) {
+                if (!(v.x == m.x && v.y == m.y)) bad_sym = 1;
+                if (!(v.x == m.x && v.y == -m.y)) bad_herm = 1;
+            } else {
+                if (!(v == m)) bad_sym = bad_herm = 1;
+            }
+        }
+    }
+    if (bad_sym) atomicAnd(flags, ~1);
+    if (bad_herm) atomicAnd(flags, ~2);
+}
+
+// =================================================================================================
 // Small helper kernels.
 // =================================================================================================
 // MODE_SPLIT: fixed-order sum of the CTA partials of launch j (ring slot) into scal[0..2]; NCCL

@@ -261,6 +261,32 @@ def test_dense_kernel_variants(orc, monkeypatch, var, tile_major, cplx):
         dm.close()
 
 
+@pytest.mark.parametrize("kind", ["real-symmetric", "hermitian", "complex-symmetric"])
+@pytest.mark.parametrize("n", [1, 2, 5, 16, 17, 127, 128, 129, 1000, 2304])
+def test_dense_symmetric_kernel(orc, monkeypatch, kind, n):
+    """A dense matrix that is bitwise equal to its (conjugate) transpose is detected at upload and multiplied by the
+    column-dot kernel (gemv_sym_kernel: flat balanced partition over warps, columns shared by two warps combined by
+    ticket).  Same answers as the general kernel (EIGSOL_B200_GEMV_SYM=0) and as the oracle; sizes around the 16-row
+    padding, the 128-element range granularity and several columns per warp."""
+    rng = np.random.default_rng(n)
+    if kind == "real-symmetric":
+        a = gen.dense_random_symmetric(n, seed=n)
+    elif kind == "hermitian":
+        a = gen.dense_random_hermitian(n, seed=n)
+    else:
+        b = rng.standard_normal((n, n)) + 1j * rng.standard_normal((n, n))
+        a = (b + b.T) / 2.0   # complex symmetric, not Hermitian
+    x0 = orc.random_unit(n, a.dtype, seed=8)
+    ref = orc.power_dense(a, x0, 12, -1.0)
+    for sym in ("1", "0"):
+        monkeypatch.setenv("EIGSOL_B200_GEMV_SYM", sym)
+        dm = es.DeviceMatrix.from_matrix(es.Matrix(a))
+        y = dm.matvec(x0)
+        assert np.max(np.abs(y - a @ x0)) <= 1e-12 * max(np.max(np.abs(a @ x0)), 1e-300)
+        check_result(dm.power(x0, es.SolverOptions(12, -1.0)), ref)
+        dm.close()
+
+
 def test_dense_nonsymmetric_colmajor_layout(orc):
     # a non-symmetric matrix catches any row/column-major mix-up; also the row-major vector constructor
     n = 37
