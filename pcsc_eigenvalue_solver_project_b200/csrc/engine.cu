@@ -255,7 +255,7 @@ struct MatrixImpl {
     int scalar_block = 256;  // EIGSOL_B200_SCALAR_BLOCK: threads per CTA (= rows per work unit) of csr_scalar
     int dense_sym = 0;  // one GPU, dense: 1 = A == A^T, 2 = A == A^H (bitwise, checked at upload) -> gemv_sym_kernel
     int64_t sym_per = 0;
-    int sym_nwarps = 0;
+    int sym_nctas = 0, sym_smem = 0;
     int gemv_map = 0;  // EIGSOL_B200_GEMV_MAP: 1 = row tiles of one column segment are neighbouring CTAs
     int gemv_var = 0;  // EIGSOL_B200_GEMV_VAR: streaming loop variant of the dense kernel (kernels.cuh)
 
@@ -1432,16 +1432,28 @@ void MatrixImpl::configure_launch() {
     block = (!dense && kernel == K_CSR_SCALAR && scalar_block == 128) ? 128 : 256;
     const int64_t s = ss();
     if (dense && dense_sym && nranks == 1) {
-        // flat, perfectly balanced partition of the stored matrix over the warps of a persistent grid (gemv_sym_kernel)
-        const int occ = dtype ? occupancy(gemv_sym_kernel<double2, 256>, 256) : occupancy(gemv_sym_kernel<double, 256>, 256);
+        // flat, perfectly balanced partition of the stored matrix over the CTAs of a persistent grid (gemv_sym_kernel)
         const int64_t total = lda * n;
-        int64_t nw = std::min<int64_t>(int64_t(sm_count) * occ * (block / 32), n);  // every warp at least one column long
-        int64_t per = ((total + nw - 1) / nw + 127) / 128 * 128;
-        per = std::max<int64_t>(per, (lda + 127) / 128 * 128);
-        nw = (total + per - 1) / per;
-        sym_per = per;
-        sym_nwarps = int(nw);
-        nslots = int((nw + block / 32 - 1) / (block / 32));
+        auto plan = [&](int64_t nc) {
+            int64_t per = ((total + nc - 1) / nc + 127) / 128 * 128;
+            return std::max<int64_t>(per, (lda + 127) / 128 * 128);  // at least one column: a column meets <= 2 CTAs
+        };
+        // the shared memory (8 warp sums per column of a range) depends on the range, the occupancy on the shared memory
+        int64_t nc = std::min<int64_t>(int64_t(sm_count) * 4, n);
+        for (int pass = 0; pass < 2; ++pass) {
+            const int64_t per = plan(nc);
+            sym_smem = int((per / lda + 3) * (block / 32) * s);
+            if (sym_smem > 48 * 1024) {
+                if (dtype) EIGSOL_CUDA(cudaFuncSetAttribute(gemv_sym_kernel<double2, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, sym_smem));
+                else EIGSOL_CUDA(cudaFuncSetAttribute(gemv_sym_kernel<double, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, sym_smem));
+            }
+            const int occ = dtype ? occupancy(gemv_sym_kernel<double2, 256>, 256, size_t(sym_smem)) : occupancy(gemv_sym_kernel<double, 256>, 256, size_t(sym_smem));
+            nc = std::min<int64_t>(int64_t(sm_count) * occ, n);
+        }
+        sym_per = plan(nc);
+        sym_smem = int((sym_per / lda + 3) * (block / 32) * s);
+        sym_nctas = int((total + sym_per - 1) / sym_per);
+        nslots = sym_nctas;
         grid = nslots + 1;
         ntiles = int(n);  // tickets: one per column
         d_dense_partial.alloc(size_t(2) * size_t(n) * size_t(s));
@@ -1598,9 +1610,9 @@ template <class S> static void launch_dense(MatrixImpl& m, int ph) {
                    m.d_dense_partial.as<S>(), m.d_tile_ticket.as<unsigned>(), m.gemv_map};
     const dim3 g(m.grid), b(B);
     if (m.dense_sym && m.nranks == 1) {
-        SymDenseView<S> V{int32_t(m.n), m.lda, m.d_dense.as<S>(), m.sym_per, m.sym_nwarps, m.d_dense_partial.as<S>(),
+        SymDenseView<S> V{int32_t(m.n), m.lda, m.d_dense.as<S>(), m.sym_per, m.sym_nctas, m.d_dense_partial.as<S>(),
                           m.d_tile_ticket.as<unsigned>(), m.dense_sym == 2 ? 1 : 0};
-        launch_pdl(m.pdl, m.stream, gemv_sym_kernel<S, B>, g, b, 0, V, it, ph);
+        launch_pdl(m.pdl, m.stream, gemv_sym_kernel<S, B>, g, b, size_t(m.sym_smem), V, it, ph);
         return;
     }
     auto go = [&](auto kern) { launch_pdl(m.pdl, m.stream, kern, g, b, 0, A, it, ph); };

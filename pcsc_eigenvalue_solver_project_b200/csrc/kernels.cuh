@@ -1161,12 +1161,13 @@ __global__ void __launch_bounds__(BLOCK) gemv_colmajor_kernel(DenseView<S> A, It
 // =================================================================================================
 // Dense GEMV for a matrix that equals its own (conjugate) transpose: y_j = sum_i op(A[i,j]) x_i, op = conj for a
 // Hermitian matrix, identity for a symmetric one -- the dot product of the STORED column j with x.  The column-major
-// array is then read as one flat stream: warp w owns the elements [w * per, (w + 1) * per) (a multiple of 128, at
-// least one column long), walks them with 32-byte loads (SASS LDG.E.ENL2.256), keeps x in L1, and reduces every column
-// with shuffles alone -- no column-segment partials of the whole vector, no shared memory, no last-CTA combine.  All
-// warps carry the same number of bytes (+-1 KB), so they finish together.  Only the column a range starts or ends in
-// the middle of is shared by two warps: its two partial sums are added, in row order, by whichever warp arrives second
-// (one ticket per column).  The engine selects this kernel when a bitwise symmetry check at upload succeeds
+// array is then read as one flat stream: CTA c owns the elements [c * per, (c + 1) * per) (a multiple of 128, at least
+// one column long) and walks them column by column in steps of 8 KB of consecutive memory (256 threads x 32-byte loads,
+// SASS LDG.E.ENL2.256), x coming from L1; a column's sum is a shuffle tree per warp plus eight warp sums parked in shared
+// memory -- one barrier per launch, no column-segment partials of the whole vector, no last-CTA combine.  All CTAs carry
+// the same number of bytes, so they finish together.  Only the column a range starts or ends in the middle of is shared
+// by two CTAs: its two partial sums are added, in row order, by whichever CTA arrives second (one ticket per column).
+// (A first version gave every WARP its own range: 4736 concurrent 4 KB streams ran 3 % slower than the general kernel.)  The engine selects this kernel when a bitwise symmetry check at upload succeeds
 // (sym_check_kernel); everything else of the launch (control CTA, state machine, epilogue sums) is the common frame.
 // One GPU only (the row blocks of a sharded dense matrix are not symmetric).
 // =================================================================================================
@@ -1174,8 +1175,8 @@ template <class S> struct SymDenseView {
     int32_t n;            // order of the matrix
     int64_t lda;          // device leading dimension (multiple of 16, rows >= n are zero)
     const S* a;           // column-major
-    int64_t per;          // elements per warp (multiple of 128, >= lda)
-    int32_t nwarps;       // warps that own a range
+    int64_t per;          // elements per CTA (multiple of 128, >= lda)
+    int32_t nctas;        // CTAs that own a range
     S* partial;           // [n][2]: partial sums of the columns shared by two warps (head part, tail part)
     unsigned* ticket;     // [n]
     int32_t conj;         // 1: Hermitian (use conj of the stored entries)
@@ -1198,83 +1199,91 @@ __global__ void __launch_bounds__(BLOCK) gemv_sym_kernel(SymDenseView<S> A, Iter
         return;
     }
     constexpr int V = 32 / int(sizeof(S));  // elements per 32-byte load: 4 real, 2 complex
-    constexpr int STEP = 32 * V;            // elements per warp instruction
+    constexpr int STEP = BLOCK * V;         // elements per CTA-wide step: 8 KB of consecutive matrix
+    constexpr int NW = BLOCK / 32;
+    extern __shared__ __align__(16) unsigned char sym_smem[];
+    S* wsum = reinterpret_cast<S*>(sym_smem);  // [columns of this CTA's range][NW]: per-warp sums, no barrier per column
     __shared__ SendSm sends;
     LaunchCtx c;
     if (!launch_begin<S>(it, phase, c)) return;
     load_sends<S>(it, c, sends);  // (no sends on one GPU; keeps the common epilogue)
     const S* __restrict__ u = ring_buf<S>(it, c.in);
     S* __restrict__ out = ring_buf<S>(it, c.out);
-    const int lane = threadIdx.x & 31;
-    const int gw = (int(blockIdx.x) - 1) * (BLOCK / 32) + (threadIdx.x >> 5);
-    double are = 0.0, aim = 0.0, qn = 0.0;
-    if (gw < A.nwarps) {
-        const int64_t total = A.lda * int64_t(A.n);
-        int64_t e = int64_t(gw) * A.per;
-        const int64_t e_end = min(total, e + A.per);
-        while (e < e_end) {
-            const int col = int(e / A.lda);
-            const int64_t r0 = e - int64_t(col) * A.lda;
-            const int64_t r1 = min(A.lda, r0 + (e_end - e));  // rows [r0, r1) of column `col`
-            const S* ap = A.a + int64_t(col) * A.lda;
-            S acc[V];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cta = int(blockIdx.x) - 1;
+    const int64_t total = A.lda * int64_t(A.n);
+    const int64_t e_begin = int64_t(cta) * A.per, e_end = min(total, e_begin + A.per);
+    const int col_first = int(e_begin / A.lda);
+    int ncols = 0;
+    for (int64_t e = e_begin; e < e_end; ++ncols) {
+        const int col = col_first + ncols;
+        const int64_t r0 = e - int64_t(col) * A.lda;
+        const int64_t r1 = min(A.lda, r0 + (e_end - e));  // rows [r0, r1) of column `col`
+        const S* ap = A.a + int64_t(col) * A.lda;
+        S acc[V];
 #pragma unroll
-            for (int k = 0; k < V; ++k) acc[k] = Sc<S>::zero();
-            int64_t i = r0 + int64_t(lane) * V;
+        for (int k = 0; k < V; ++k) acc[k] = Sc<S>::zero();
 #pragma unroll 4
-            for (; i + V <= r1; i += STEP) {
-                S a[V], x[V];
-                ld_stream_row4<S>(ap + i, a);
-                {
-                    // the matching 32 bytes of x, through L1 (x is read by every warp over and over)
-                    const double2* xp = reinterpret_cast<const double2*>(u + i);
-                    const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
-                    if constexpr (Sc<S>::is_complex) {
-                        x[0] = xa;
-                        x[1] = xb;
-                    } else {
-                        x[0] = xa.x;
-                        x[1] = xa.y;
-                        x[2] = xb.x;
-                        x[3] = xb.y;
-                    }
-                }
-#pragma unroll
-                for (int k = 0; k < V; ++k) {
-                    if constexpr (Sc<S>::is_complex) {
-                        if (A.conj) a[k].y = -a[k].y;
-                    }
-                    Sc<S>::mac(acc[k], a[k], x[k]);
+        for (int64_t i = r0 + int64_t(threadIdx.x) * V; i + V <= r1; i += STEP) {
+            S a[V], x[V];
+            ld_stream_row4<S>(ap + i, a);
+            {
+                // the matching 32 bytes of x, through L1 (x is read by every CTA over and over)
+                const double2* xp = reinterpret_cast<const double2*>(u + i);
+                const double2 xa = __ldg(xp), xb = __ldg(xp + 1);
+                if constexpr (Sc<S>::is_complex) {
+                    x[0] = xa;
+                    x[1] = xb;
+                } else {
+                    x[0] = xa.x;
+                    x[1] = xa.y;
+                    x[2] = xb.x;
+                    x[3] = xb.y;
                 }
             }
-            S sum = acc[0];
 #pragma unroll
-            for (int k = 1; k < V; ++k) Sc<S>::add(sum, acc[k]);
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) Sc<S>::add(sum, Sc<S>::shfl_down(sum, d, 32));
-            if (lane == 0) {
-                const bool head = r0 == 0, tail = r1 == A.lda;
-                bool finalize = head && tail;
-                S z = sum;
-                if (!finalize) {
-                    // a column shared with the neighbouring warp: the second to arrive adds head + tail (row order)
-                    A.partial[2 * int64_t(col) + (head ? 0 : 1)] = sum;
-                    __threadfence();
-                    const unsigned t = atomicAdd(A.ticket + col, 1u);
-                    if (t == 1u) {
-                        A.ticket[col] = 0;
-                        __threadfence();
-                        z = Sc<S>::ldcg(A.partial + 2 * int64_t(col));
-                        Sc<S>::add(z, Sc<S>::ldcg(A.partial + 2 * int64_t(col) + 1));
-                        finalize = true;
-                    }
+            for (int k = 0; k < V; ++k) {
+                if constexpr (Sc<S>::is_complex) {
+                    if (A.conj) a[k].y = -a[k].y;
                 }
-                if (finalize) row_epilogue<S>(sends, Sc<S>::scale(z, c.s), Sc<S>::ldg(u + col), out, col, are, aim, qn);
+                Sc<S>::mac(acc[k], a[k], x[k]);
             }
-            e += r1 - r0;
         }
+        S sum = acc[0];
+#pragma unroll
+        for (int k = 1; k < V; ++k) Sc<S>::add(sum, acc[k]);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) Sc<S>::add(sum, Sc<S>::shfl_down(sum, d, 32));
+        if (lane == 0) wsum[ncols * NW + warp] = sum;
+        e += r1 - r0;
     }
-    cta_finish<S, BLOCK>(it, c, are, aim, qn, blockIdx.x - 1);
+    __syncthreads();
+    // thread t finishes column col_first + t of the range: the NW warp sums in warp order, then -- for the (at most two)
+    // columns shared with a neighbouring CTA -- head + tail in row order by whichever CTA arrives second
+    double are = 0.0, aim = 0.0, qn = 0.0;
+    for (int t = threadIdx.x; t < ncols; t += BLOCK) {
+        S z = Sc<S>::zero();
+#pragma unroll
+        for (int w = 0; w < NW; ++w) Sc<S>::add(z, wsum[t * NW + w]);
+        const int col = col_first + t;
+        const int64_t cs = int64_t(col) * A.lda;
+        const bool head = cs >= e_begin, tail = cs + A.lda <= e_end;  // the range holds the column's first / last row
+        bool finalize = head && tail;
+        if (!finalize) {
+            A.partial[2 * int64_t(col) + (head ? 0 : 1)] = z;
+            __threadfence();
+            const unsigned tk = atomicAdd(A.ticket + col, 1u);
+            if (tk == 1u) {
+                A.ticket[col] = 0;
+                __threadfence();
+                z = Sc<S>::ldcg(A.partial + 2 * int64_t(col));
+                Sc<S>::add(z, Sc<S>::ldcg(A.partial + 2 * int64_t(col) + 1));
+                finalize = true;
+            }
+        }
+        if (finalize) row_epilogue<S>(sends, Sc<S>::scale(z, c.s), Sc<S>::ldg(u + col), out, col, are, aim, qn);
+    }
+    cta_finish<S, BLOCK>(it, c, are, aim, qn, cta);
 }
 
 // Bitwise test A == A^T (flags bit 0 cleared if not) and A == A^H (bit 1 cleared if not) of a column-major n x n matrix:
