@@ -1376,7 +1376,9 @@ void MatrixImpl::init_dense(int64_t rows, const void* a, int64_t lda_host) {
 // the stored columns as rows (gemv_sym_kernel).  EIGSOL_B200_GEMV_SYM=0 switches the test (and that kernel) off.
 void MatrixImpl::check_dense_symmetry() {
     dense_sym = 0;
-    if (nranks != 1 || n < 1 || !env_int("EIGSOL_B200_GEMV_SYM", 1)) return;
+    // Off by default: measured on C3 (8192^2, symmetric), the column-dot kernel runs 92.3 us per trip against 89.1 us of
+    // the general kernel -- the launch boundary, not the streaming pattern, is what both lose (profiles/r02_notes.md).
+    if (nranks != 1 || n < 1 || !env_int("EIGSOL_B200_GEMV_SYM", 0)) return;
     DevBuf d_flags;
     d_flags.alloc(64);
     int three = 3;
