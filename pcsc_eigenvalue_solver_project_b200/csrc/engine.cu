@@ -362,12 +362,16 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
     {
         // the device's stream-ordered pool keeps what an ingest frees (up to EIGSOL_B200_POOL_KEEP_MB, default 16 GB of
         // the 180) so that the next upload of a matrix does not pay the driver for its buffers again
-        cudaMemPool_t pool = nullptr;
-        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) {
-            uint64_t keep = uint64_t(std::max(0, env_int("EIGSOL_B200_POOL_KEEP_MB", 16384))) << 20;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        static std::atomic<uint64_t> done_mask{0};  // once per device and process
+        const uint64_t bit = uint64_t(1) << (device & 63);
+        if (!(done_mask.fetch_or(bit) & bit)) {
+            cudaMemPool_t pool = nullptr;
+            if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) {
+                uint64_t keep = uint64_t(std::max(0, env_int("EIGSOL_B200_POOL_KEEP_MB", 16384))) << 20;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            }
+            cudaGetLastError();
         }
-        cudaGetLastError();
     }
     EIGSOL_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     EIGSOL_CUDA(cudaEventCreate(&ev0));
@@ -2645,6 +2649,31 @@ extern "C" int eigsol_b200_hbm_probe(int64_t plane_bytes, int planes, int reps, 
 // ---- one-shot entry points ------------------------------------------------------------------------
 extern "C" {
 
+// The caller's result vector is usually fresh memory (np.empty, Eigen's Vector(n)): the download's first touch of its
+// pages costs more than the PCIe copy (134 MB: 5-9 ms of page faults, worse with several ranks writing at once).  The
+// one-shot calls touch the pages -- writing back what is there -- on a few helper threads while the matrix uploads.
+struct Prefault {
+    std::vector<std::thread> pool;
+    void start(void* p, size_t bytes) {
+        if (!p || bytes < (size_t(32) << 20) || !env_int("EIGSOL_B200_PREFAULT", 1)) return;
+        const int nt = 4;
+        char* base = static_cast<char*>(p);
+        for (int t = 0; t < nt; ++t)
+            pool.emplace_back([=] {
+                const size_t lo = bytes * size_t(t) / nt, hi = bytes * size_t(t + 1) / nt;
+                for (size_t off = lo; off < hi; off += 4096) {
+                    volatile char* q = base + off;
+                    *q = *q;
+                }
+            });
+    }
+    void join() {
+        for (auto& t : pool) t.join();
+        pool.clear();
+    }
+    ~Prefault() { join(); }
+};
+
 // Solve and, if keep_out != NULL, hand the device-resident matrix to the caller instead of destroying it: the FIRST
 // solve on a matrix and its upload are one call (the start vector rides on the matrix upload), later solves use
 // eigsol_b200_power_run on *keep_out.
@@ -2653,9 +2682,12 @@ int eigsol_b200_power_csc_keep(int dtype, int64_t rows, int64_t cols, const int3
                                double lambda_out[2], int* iterations_out, int* converged_out, eigsol_b200_matrix** keep_out) {
     if (keep_out) *keep_out = nullptr;
     eigsol_b200_matrix* m = nullptr;
+    Prefault pf;
+    if (rows > 0 && (dtype == EIGSOL_B200_F64 || dtype == EIGSOL_B200_C128)) pf.start(x_out, size_t(rows) * (dtype ? 16 : 8));
     g_preload_x0 = x0;  // the start vector goes up together with the matrix (single GPU)
     int e = eigsol_b200_matrix_create_csc(dtype, rows, cols, outer, inner, values, nullptr, &m);
     g_preload_x0 = nullptr;
+    pf.join();
     if (e) return e;
     e = eigsol_b200_power_run(m, x0, max_iterations, tolerance, x_out, lambda_out, iterations_out, converged_out);
     if (!e && keep_out) {

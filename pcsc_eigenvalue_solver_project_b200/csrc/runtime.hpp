@@ -7,8 +7,10 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 namespace eigsol_b200 {
 
@@ -113,18 +115,55 @@ struct DevBuf {
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
 
+// Small pinned host blocks (the 200-byte iteration state a handle polls) are recycled for the life of the process:
+// cudaMallocHost takes a process-wide driver lock and milliseconds -- per handle, and serialised over the rank
+// threads of a group, it was most of a group handle's 9-11 ms of "streams + state" set-up.
+struct SmallPinnedPool {
+    static constexpr size_t kBytes = 4096;
+    std::mutex mu;
+    std::vector<void*> idle;
+    static SmallPinnedPool& get() {
+        static SmallPinnedPool* p = new SmallPinnedPool;  // never destroyed: blocks may be returned during static destruction
+        return *p;
+    }
+    void* acquire() {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            if (!idle.empty()) {
+                void* q = idle.back();
+                idle.pop_back();
+                return q;
+            }
+        }
+        void* q = nullptr;
+        EIGSOL_CUDA(cudaHostAlloc(&q, kBytes, cudaHostAllocPortable));
+        return q;
+    }
+    void release(void* q) {
+        std::lock_guard<std::mutex> lk(mu);
+        idle.push_back(q);
+    }
+};
+
 struct PinnedBuf {
     void* p = nullptr;
+    bool small = false;
     PinnedBuf() = default;
     PinnedBuf(const PinnedBuf&) = delete;
     PinnedBuf& operator=(const PinnedBuf&) = delete;
-    ~PinnedBuf() {
-        if (p) cudaFreeHost(p);
+    ~PinnedBuf() { release(); }
+    void release() {
+        if (p) {
+            if (small) SmallPinnedPool::get().release(p);
+            else cudaFreeHost(p);
+        }
+        p = nullptr;
     }
     void alloc(size_t n) {
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        EIGSOL_CUDA(cudaMallocHost(&p, n));
+        release();
+        small = n <= SmallPinnedPool::kBytes;
+        if (small) p = SmallPinnedPool::get().acquire();
+        else EIGSOL_CUDA(cudaMallocHost(&p, n));
     }
     template <class T> T* as() const { return static_cast<T*>(p); }
 };
