@@ -193,6 +193,10 @@ def test_group_rejects_malformed_input_and_recovers(orc, ngpu):
     bad[len(bad) // 2] = n + 7
     with pytest.raises(ValueError, match="inner index out of range"):
         es.DeviceMatrix.from_matrix(es.Matrix(((n, n), outer, bad, cv)))
+    bad_outer = outer.copy()
+    bad_outer[n // 3], bad_outer[n // 3 + 1] = bad_outer[n // 3 + 1], bad_outer[n // 3]   # not monotone inside one slab
+    with pytest.raises(ValueError, match="outer index not monotone"):
+        es.DeviceMatrix.from_matrix(es.Matrix(((n, n), bad_outer, inner, cv)))
     x0 = orc.random_unit(n, np.float64, seed=9)
     check(es.powerMethod(es.Matrix(((n, n), outer, inner, cv)), es.SolverOptions(25, -1.0), x0=x0),
           orc.power_csc((n, n), outer, inner, cv, x0, 25, -1.0))
