@@ -375,7 +375,13 @@ def main():
         dist = None
         if rank != 0:
             return
-        time.sleep(1.0)  # the other ranks' processes exit; outside every timed region
+        try:
+            import torch
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()
+        except Exception:
+            pass
+        time.sleep(3.0)  # the other ranks' processes tear down NCCL / CUDA and exit; outside every timed region
     e2e = None
     if not args.no_e2e:
         opts = es.SolverOptions(args.steps, -1.0)
