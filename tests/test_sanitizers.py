@@ -39,3 +39,18 @@ def test_control_state_machine_under_asan_ubsan(tmp_path):
                        env=dict(ENV, ASAN_OPTIONS="detect_leaks=0:protect_shadow_gap=0"))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "no sanitizer report" in r.stdout
+
+
+def test_group_meeting_point_under_thread_sanitizer(tmp_path):
+    """csrc/group.hpp (barrier / exchange / abort / reset of the host threads of a single-process GPU group) under
+    ThreadSanitizer: 2, 3 and 8 threads, 2000 exchange rounds each, a failing rank, a reset."""
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.isdir(cuda_inc):
+        pytest.skip("CUDA headers not available")
+    exe = str(tmp_path / "group_tsan")
+    r = subprocess.run(["g++", "-std=c++17", "-g", "-O1", "-fsanitize=thread", "-pthread", f"-I{cuda_inc}",
+                        os.path.join(ROOT, "tests", "sanitize", "group_tsan.cpp"), "-o", exe, "-ldl"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600, env=dict(os.environ, TSAN_OPTIONS="halt_on_error=1"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "no sanitizer report" in r.stdout
