@@ -332,6 +332,7 @@ void MatrixImpl::init_common(int dtype_, Comm* comm_) {
         }
     }
     EIGSOL_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    g_alloc_stream = stream;  // small buffers of this handle: from the pool, on its stream (the API call's AllocScope restores)
     EIGSOL_CUDA(cudaEventCreate(&ev0));
     EIGSOL_CUDA(cudaEventCreate(&ev1));
     d_state.alloc(sizeof(PowerState));
@@ -2202,8 +2203,15 @@ struct eigsol_b200_matrix {
     const MatrixImpl& lead() const { return group ? *group->ranks[0] : *one; }
     // runs f(rank impl) on the handle's rank(s)
     template <class F> void each(F&& f) {
-        if (group) group->run_all([&](int r) { f(*group->ranks[size_t(r)], r); });
-        else f(*one, 0);
+        if (group) {
+            group->run_all([&](int r) {
+                AllocScope sc(group->ranks[size_t(r)]->stream);
+                f(*group->ranks[size_t(r)], r);
+            });
+        } else {
+            AllocScope sc(one->stream);
+            f(*one, 0);
+        }
     }
 };
 struct eigsol_b200_comm {
@@ -2318,6 +2326,7 @@ int eigsol_b200_matrix_create_csc(int dtype, int64_t rows, int64_t cols, const i
             return int(EIGSOL_B200_OK);
         }
         Trace tr0;
+        AllocScope alloc_scope(nullptr);  // init_common makes the handle's stream current for small allocations
         h->one.reset(new MatrixImpl);
         MatrixImpl& m = *h->one;
         m.init_common(dtype, comm ? &comm->impl : nullptr);
@@ -2382,6 +2391,7 @@ int eigsol_b200_matrix_create_csr_rows(int dtype, int64_t n, int64_t row_begin, 
             ++g_matrices_created;
             return int(EIGSOL_B200_OK);
         }
+        AllocScope alloc_scope(nullptr);  // init_common makes the handle's stream current for small allocations
         h->one.reset(new MatrixImpl);
         MatrixImpl& m = *h->one;
         m.init_common(dtype, comm ? &comm->impl : nullptr);

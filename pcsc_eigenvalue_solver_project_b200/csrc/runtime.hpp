@@ -33,6 +33,18 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 }
 #define EIGSOL_CUDA(call) ::eigsol_b200::cuda_check((call), #call, __FILE__, __LINE__)
 
+// Stream the small zero-filled device buffers of the calling thread come from (DevBuf::alloc): the handle's own
+// non-blocking stream while one of its operations runs on this thread, else none (plain cudaMalloc).  With peer access
+// enabled between 8 GPUs every cudaMalloc / cudaFree maps or unmaps the block on all peers under a process-wide lock
+// (~0.6 ms each, serialised over the rank threads: 10 + 9 + 17 ms of an 8-GPU group's set-up and tear-down were ~30 small
+// allocations); the stream-ordered pool hands the same blocks out again for nothing.
+inline thread_local cudaStream_t g_alloc_stream = nullptr;
+struct AllocScope {
+    cudaStream_t prev;
+    explicit AllocScope(cudaStream_t s) : prev(g_alloc_stream) { g_alloc_stream = s; }
+    ~AllocScope() { g_alloc_stream = prev; }
+};
+
 // ---- RAII device / pinned memory ---------------------------------------------------------------
 struct DevBuf {
     void* p = nullptr;
@@ -98,10 +110,27 @@ struct DevBuf {
         EIGSOL_CUDA(cudaMemset(p, 0, n + pad));
         EIGSOL_CUDA(cudaDeviceSynchronize());
     }
-    // The default for small buffers: plain, zero-filled, synchronised.  (Routing these through cudaMallocAsync on the
-    // calling thread's per-thread stream was measured on a 2-GPU group: the setup phase that allocates the mailboxes
-    // went from 0.4 ms to 32 ms -- per-thread streams synchronise with the legacy stream the plain copies use.)
-    void alloc(size_t n, size_t pad = 64) { alloc_plain(n, pad); }
+    // The default for small buffers: zero-filled and ready for use on any stream when the call returns.  From the
+    // device's stream-ordered pool on the handle's own stream when one is current on this thread (g_alloc_stream), else
+    // plain.  (Routing these through cudaStreamPerThread instead was measured: the peer-map phase of a 2-GPU group went
+    // from 0.4 ms to 32 ms -- per-thread streams synchronise with the legacy stream the plain copies use.)
+    void alloc(size_t n, size_t pad = 64) {
+        if (!g_alloc_stream) {
+            alloc_plain(n, pad);
+            return;
+        }
+        release();
+        bytes = n;
+        if (cudaMallocAsync(&p, n + pad, g_alloc_stream) != cudaSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+            alloc_plain(n, pad);
+            return;
+        }
+        pooled = true;
+        EIGSOL_CUDA(cudaMemsetAsync(p, 0, n + pad, g_alloc_stream));
+        EIGSOL_CUDA(cudaStreamSynchronize(g_alloc_stream));
+    }
     // no zero fill, no synchronisation: for buffers every byte of which is written before it is read
     void alloc_raw(size_t n, size_t pad = 64) {
         release();
