@@ -382,6 +382,14 @@ def main():
         except Exception:
             pass
         time.sleep(3.0)  # the other ranks' processes tear down NCCL / CUDA and exit; outside every timed region
+        # NCCL / the launcher may have narrowed this process's CPU affinity to the cores next to GPU 0; the library's
+        # uploader threads (one set per GPU) inherit it.  The one-process leg gets the whole host back.
+        try:
+            affinity_before = len(os.sched_getaffinity(0))
+            os.sched_setaffinity(0, range(os.cpu_count()))
+            sys.stderr.write(f"bench.py: CPU affinity {affinity_before} -> {len(os.sched_getaffinity(0))} cores\n")
+        except Exception as exc:
+            sys.stderr.write(f"bench.py: sched_setaffinity: {exc}\n")
     e2e = None
     if not args.no_e2e:
         opts = es.SolverOptions(args.steps, -1.0)
