@@ -254,6 +254,49 @@ def emit(line: dict):
         os.write(_REAL_STDOUT, data)
 
 
+def e2e_leg(name, steps, ngpu, host=None):
+    """The reference-facing call with HOST buffers, timed end to end: powerMethod(Matrix, SolverOptions{steps, -1}) in
+    ONE process -- matrix + x0 uploaded, CSC -> CSR, `steps` trips, eigenvector downloaded.  With ngpu > 1 the library
+    shards the call over the first ngpu devices itself (EIGSOL_B200_NGPU).  One untimed 1-trip call of the same API runs
+    first (CUDA contexts of the group's devices, pinned staging buffers and the device memory pool are warm, as they are
+    for any caller's second solve); each call gets its own Matrix (a Matrix keeps its device copy, and the timed call
+    must upload)."""
+    import pcsc_eigenvalue_solver_project_b200 as es
+    from pcsc_eigenvalue_solver_project_b200 import generators as gen
+    n = workload_order(name)
+    dt = np.complex128 if DTYPES[name] == "c128" else np.float64
+    x0 = es.random_unit(n, dt, seed=1)
+    if name == "c3":
+        a = host["a"] if host else gen.dense_random_symmetric(n)
+        mk = lambda: es.Matrix(a)
+        h2d = a.nbytes + x0.nbytes
+    else:
+        if host and "rp" in host and host.get("whole"):
+            rp, ci, v = host["rp"], host["ci"], host["v"]
+        else:
+            _, rp, ci, v = workload_rows(name, gen)
+        outer, inner, vals = gen.csr_to_csc_hermitian(rp, ci, v)
+        del rp, ci, v
+        mk = lambda: es.Matrix(((n, n), outer, inner, vals))
+        h2d = outer.nbytes + inner.nbytes + vals.nbytes + x0.nbytes
+    os.environ["EIGSOL_B200_NGPU"] = str(ngpu)
+    try:
+        es.powerMethod(mk(), es.SolverOptions(1, -1.0), x0=x0)
+        M = mk()
+        t0 = time.perf_counter()
+        r = es.powerMethod(M, es.SolverOptions(steps, -1.0), x0=x0)
+        t_e2e = time.perf_counter() - t0
+    finally:
+        os.environ["EIGSOL_B200_NGPU"] = "1"
+    assert r.iterations == steps
+    del M
+    return {"value": steps / t_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d / steps,
+            "d2h_bytes_per_step": x0.nbytes / steps, "seconds": t_e2e, "lambda": repr(r.eigenvalue),
+            "call": "powerMethod(Matrix, SolverOptions{steps, -1}) one-shot in one process: matrix + x0 uploaded, "
+                    "CSC->CSR, steps trips, eigenvector downloaded (after one untimed 1-trip call of the same API)" +
+                    (f"; EIGSOL_B200_NGPU={ngpu}: the library shards the call over {ngpu} GPUs" if ngpu > 1 else "")}
+
+
 def main():
     quiet_stdout()
     ap = argparse.ArgumentParser()
@@ -264,12 +307,16 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("BENCH_WORKLOAD", "c5"), choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-child", type=int, default=0, help=argparse.SUPPRESS)  # internal: run only the e2e leg on N GPUs
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.e2e_child:
+        emit(e2e_leg(args.workload, args.steps, args.e2e_child))
+        return
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
@@ -392,48 +439,29 @@ def main():
             sys.stderr.write(f"bench.py: sched_setaffinity: {exc}\n")
     e2e = None
     if not args.no_e2e:
-        opts = es.SolverOptions(args.steps, -1.0)
-        M = None
-        if rank == 0:
-            if name == "c3":
-                M = es.Matrix(host["a"])  # the reference's Matrix also stores by value (matrix.hpp:187-195)
-                h2d = host["a"].nbytes + x0.nbytes
+        try:
+            if world == 1:
+                e2e = e2e_leg(name, args.steps, 1, dict(host, whole=True))
             else:
-                if world > 1:
-                    _, rp, ci, v = workload_rows(name, gen)
-                else:
-                    rp, ci, v = host["rp"], host["ci"], host["v"]
-                outer, inner, vals = gen.csr_to_csc_hermitian(rp, ci, v)
-                M = es.Matrix(((n, n), outer, inner, vals))
-                h2d = outer.nbytes + inner.nbytes + vals.nbytes + x0.nbytes
-                del rp, ci, v
-        cpu_barrier()
-        if rank == 0:
-          try:
-              os.environ["EIGSOL_B200_NGPU"] = str(world)
-              # one untimed call of the same API first (one trip): CUDA contexts of the group's devices, pinned staging
-              # buffers and the device memory pool are warm, as they are for any caller's second solve
-              # (each call gets its own Matrix: a Matrix keeps its device copy, and the timed call must upload)
-              mk = (lambda: es.Matrix(host["a"])) if name == "c3" else (lambda: es.Matrix(((n, n), outer, inner, vals)))
-              M = None
-              es.powerMethod(mk(), es.SolverOptions(1, -1.0), x0=x0)
-              M = mk()
-              t0 = time.perf_counter()
-              r = es.powerMethod(M, opts, x0=x0)
-              t_e2e = time.perf_counter() - t0
-              os.environ["EIGSOL_B200_NGPU"] = "1"
-              assert r.iterations == args.steps
-              e2e = {"value": args.steps / t_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d / args.steps,
-                     "d2h_bytes_per_step": x0.nbytes / args.steps, "seconds": t_e2e, "lambda": repr(r.eigenvalue),
-                     "call": "powerMethod(Matrix, SolverOptions{steps, -1}) one-shot in one process: matrix + x0 uploaded, "
-                             "CSC->CSR, steps trips, eigenvector downloaded (after one untimed 1-trip call of the same API)" +
-                             (f"; EIGSOL_B200_NGPU={world}: the library shards the call over {world} GPUs" if world > 1 else "")}
-              del M
-          except Exception as exc:  # the device-resident figure must survive a failure of the end-to-end leg
-              os.environ["EIGSOL_B200_NGPU"] = "1"
-              sys.stderr.write(f"bench.py: e2e leg failed: {type(exc).__name__}: {exc}\n")
-              e2e = None
-        cpu_barrier()
+                # A clean child process makes the call (the launcher's variables removed): inside this process -- after
+                # torch.distributed / NCCL and the per-rank matrices -- the very same call measured 55-73 ms on 2 GPUs
+                # against 43-47 ms from a fresh process, one GPU's upload running at half speed; the cause was not
+                # found (CPU affinity, torch, NCCL and OMP_NUM_THREADS were ruled out, profiles/r02_notes.md).
+                env = {k: v for k, v in os.environ.items()
+                       if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK",
+                                    "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS", "TORCHELASTIC_RUN_ID")
+                       and not k.startswith("TORCHELASTIC_") and not k.startswith("NCCL_ASYNC")}
+                del host
+                p = subprocess.run([sys.executable, os.path.abspath(__file__), "--e2e-child", str(world), "--workload", name,
+                                    "--steps", str(args.steps)], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                                   text=True, timeout=900)
+                if p.returncode != 0:
+                    raise RuntimeError(f"e2e child failed ({p.returncode}): {p.stderr[-600:]}")
+                e2e = json.loads(p.stdout.strip().splitlines()[-1])
+                e2e["call"] += "; made from a fresh child process of rank 0 after the other ranks have left"
+        except Exception as exc:  # the device-resident figure must survive a failure of the end-to-end leg
+            sys.stderr.write(f"bench.py: e2e leg failed: {type(exc).__name__}: {exc}\n")
+            e2e = None
 
     cpu_baseline = None
     parity = None

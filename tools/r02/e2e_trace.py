@@ -10,6 +10,19 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspa
 import pcsc_eigenvalue_solver_project_b200 as es
 from pcsc_eigenvalue_solver_project_b200 import generators as gen
 
+if os.environ.get("TRACE_TORCH"):  # diagnosis: does a torch CUDA context / an NCCL process group in the process change the upload?
+    import torch
+    torch.cuda.set_device(0)
+    torch.zeros(1, device="cuda")
+    if os.environ["TRACE_TORCH"] == "nccl":
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29655")
+        dist.init_process_group(backend="nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+        t = torch.zeros(4, device="cuda")
+        dist.all_reduce(t)
+        torch.cuda.synchronize()
+        dist.destroy_process_group()
 g = int(os.environ.get("GRID", 256))
 n = g ** 3
 rp, ci, v = gen.laplacian_3d(g)
