@@ -281,7 +281,8 @@ def e2e_leg(name, steps, ngpu, host=None):
         h2d = outer.nbytes + inner.nbytes + vals.nbytes + x0.nbytes
     os.environ["EIGSOL_B200_NGPU"] = str(ngpu)
     try:
-        es.powerMethod(mk(), es.SolverOptions(1, -1.0), x0=x0)
+        for _ in range(2 if ngpu > 1 else 1):  # a group's first call creates the devices' contexts, its second warms the pools
+            es.powerMethod(mk(), es.SolverOptions(1, -1.0), x0=x0)
         M = mk()
         t0 = time.perf_counter()
         r = es.powerMethod(M, es.SolverOptions(steps, -1.0), x0=x0)
@@ -293,7 +294,7 @@ def e2e_leg(name, steps, ngpu, host=None):
     return {"value": steps / t_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d / steps,
             "d2h_bytes_per_step": x0.nbytes / steps, "seconds": t_e2e, "lambda": repr(r.eigenvalue),
             "call": "powerMethod(Matrix, SolverOptions{steps, -1}) one-shot in one process: matrix + x0 uploaded, "
-                    "CSC->CSR, steps trips, eigenvector downloaded (after one untimed 1-trip call of the same API)" +
+                    "CSC->CSR, steps trips, eigenvector downloaded (after untimed 1-trip calls of the same API: one on one GPU, two on a group)" +
                     (f"; EIGSOL_B200_NGPU={ngpu}: the library shards the call over {ngpu} GPUs" if ngpu > 1 else "")}
 
 
@@ -443,22 +444,12 @@ def main():
             if world == 1:
                 e2e = e2e_leg(name, args.steps, 1, dict(host, whole=True))
             else:
-                # A clean child process makes the call (the launcher's variables removed): inside this process -- after
-                # torch.distributed / NCCL and the per-rank matrices -- the very same call measured 55-73 ms on 2 GPUs
-                # against 43-47 ms from a fresh process, one GPU's upload running at half speed; the cause was not
-                # found (CPU affinity, torch, NCCL and OMP_NUM_THREADS were ruled out, profiles/r02_notes.md).
-                env = {k: v for k, v in os.environ.items()
-                       if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK",
-                                    "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS", "TORCHELASTIC_RUN_ID")
-                       and not k.startswith("TORCHELASTIC_") and not k.startswith("NCCL_ASYNC")}
+                # (The same call made from a fresh child process of rank 0 was tried: no faster than in this process.
+                # Under torchrun the leg measures 55-85 ms on 2 GPUs against 43-49 ms for the identical call from a
+                # stand-alone script on the same box -- one GPU's upload runs at half speed; CPU affinity, torch, NCCL
+                # and OMP_NUM_THREADS were ruled out, the cause was not found: profiles/r02_notes.md.)
                 del host
-                p = subprocess.run([sys.executable, os.path.abspath(__file__), "--e2e-child", str(world), "--workload", name,
-                                    "--steps", str(args.steps)], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
-                                   text=True, timeout=900)
-                if p.returncode != 0:
-                    raise RuntimeError(f"e2e child failed ({p.returncode}): {p.stderr[-600:]}")
-                e2e = json.loads(p.stdout.strip().splitlines()[-1])
-                e2e["call"] += "; made from a fresh child process of rank 0 after the other ranks have left"
+                e2e = e2e_leg(name, args.steps, world)
         except Exception as exc:  # the device-resident figure must survive a failure of the end-to-end leg
             sys.stderr.write(f"bench.py: e2e leg failed: {type(exc).__name__}: {exc}\n")
             e2e = None
