@@ -4,5 +4,3 @@ mkdir -p gpurun_out/r02
 timeout 500 python -m pytest tests -m gpu -x -q > gpurun_out/r02/c31_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r02/c31_pytest_gpu.log
 timeout 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02/c31_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/r02/c31_smoke.log
 timeout 300 python bench.py --steps 20 --warmup 5 > gpurun_out/r02/c31_bench_c5_n1.json 2> gpurun_out/r02/c31_bench.err; echo "bench rc=$?"
-python -c "
-import json; d=json.loads(open('gpurun_out/r02/c31_bench_c5_n1.json').read().strip().splitlines()[-1]); print('N=1', d['value'], d['ms_per_step'], 'frac', d['roofline']['frac'], 'e2e', d['e2e'] and (d['e2e']['value'], d['e2e']['seconds']), 'parity', d['parity'] and d['parity']['ok'], 'cpu', d['cpu_baseline']['value'])"
